@@ -1,0 +1,195 @@
+/* neptune_rt.h — C ABI of the B200 runtime behind the `neptuneir-to-b200` pipeline.
+ *
+ * This is the drop-in boundary for the one hot path this project accelerates: the
+ * `neptune_ir.apply` stencil sweep.  In the reference that op is lowered by
+ * `ApplyToSCFForLowering::matchAndRewrite` (lib/Passes/DataflowLowering.cpp:258-448) into a
+ * malloc + memref.copy + scalar scf.for nest, and `neptune_ir.store` into a second full copy
+ * (lib/Passes/DataflowLowering.cpp:165-220).  Here the same semantics are executed by
+ * hand-written sm_100a kernels; a pass emits calls to the functions below the way
+ * lib/Passes/RuntimeLowering.cpp:39-53,169-178 emits calls to `_neptune_rt_runtime_*`
+ * (declared in include/Runtime/PETSc/NeptunePETScRuntime.h:79-105).
+ *
+ * Conventions (contrast with the reference shim):
+ *   - plain C, opaque handles + POD out-params, never a struct returned by value;
+ *   - every function returns 0 on success, a negative NEPTUNE_RT_E* code on failure, and
+ *     leaves a message retrievable with neptune_rt_last_error();
+ *   - every *_alloc / *_create has a matching *_free / *_destroy; the ctx owns streams,
+ *     scratch memory and the NCCL communicator;
+ *   - one host thread drives one ctx (one process per GPU); a ctx is not thread-safe;
+ *   - there is NO CPU fallback: without a CUDA device neptune_rt_init fails.
+ *
+ * Normative semantics of one sweep (from DataflowLowering.cpp:258-448):
+ *   out[q] = in0[q]                      for every q of the result box,
+ *   out[p - out_lb] = body(in_k[p + off - in_lb_k] ...)   for every p in [lb, ub),
+ * the body being the scalar op list of the apply region evaluated op by op, in the body's own
+ * order, IEEE-754 round-to-nearest, no contraction (unless the stencil is created with
+ * NEPTUNE_RT_FLAG_FMA, which moves the result to the 1e-12 tolerance tier).
+ */
+#ifndef NEPTUNE_RT_H
+#define NEPTUNE_RT_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define NEPTUNE_RT_MAX_RANK 3
+#define NEPTUNE_RT_MAX_INPUTS 32
+#define NEPTUNE_RT_MAX_CONSTS 64
+
+/* status codes */
+#define NEPTUNE_RT_OK 0
+#define NEPTUNE_RT_EINVAL (-1)      /* bad argument / malformed descriptor              */
+#define NEPTUNE_RT_ENODEV (-2)      /* no CUDA device / driver (there is no CPU path)   */
+#define NEPTUNE_RT_ECUDA (-3)       /* a CUDA call failed                               */
+#define NEPTUNE_RT_EUNSUPPORTED (-4)/* body is outside the compiled stencil catalogue   */
+#define NEPTUNE_RT_ENCCL (-5)       /* NCCL missing or a collective failed              */
+#define NEPTUNE_RT_ENOMEM (-6)
+
+/* element types: FieldType/TempType `element` (include/Dialect/NeptuneIR/NeptuneIRTypes.td:12-59) */
+#define NEPTUNE_RT_F32 0
+#define NEPTUNE_RT_F64 1
+
+/* body op codes: neptune_ir.access (NeptuneIROps.td:205-228) plus the float part of the
+ * linear-body whitelist of lib/Passes/VerifyAndAnnotate.cpp:167-204 */
+#define NEPTUNE_RT_OP_ACCESS 0
+#define NEPTUNE_RT_OP_CONST 1
+#define NEPTUNE_RT_OP_ADD 2
+#define NEPTUNE_RT_OP_SUB 3
+#define NEPTUNE_RT_OP_MUL 4
+#define NEPTUNE_RT_OP_DIV 5
+#define NEPTUNE_RT_OP_NEG 6
+
+/* One scalar op of the apply region.  The result of op i is value number i. */
+typedef struct neptune_rt_body_op {
+  int32_t opcode;                        /* NEPTUNE_RT_OP_*                                 */
+  int32_t a, b;                          /* operand value numbers (ADD..NEG), else -1       */
+  int32_t input;                         /* ACCESS: which apply input                       */
+  int64_t offset[NEPTUNE_RT_MAX_RANK];   /* ACCESS: constant neighbour offset, logical dims */
+  double value;                          /* CONST: literal (already rounded to the dtype)   */
+} neptune_rt_body_op;
+
+/* Everything `ApplyOp` (NeptuneIROps.td:164-197) carries that the lowering reads. */
+typedef struct neptune_rt_stencil_desc {
+  int32_t rank;                          /* 1..3                                            */
+  int32_t dtype;                         /* NEPTUNE_RT_F32 / F64                            */
+  int32_t n_inputs;                      /* variadic temp inputs                            */
+  int32_t n_ops;
+  const neptune_rt_body_op *ops;         /* body in program order                           */
+  int32_t yield_value;                   /* value number passed to neptune_ir.yield         */
+  int32_t flags;                         /* NEPTUNE_RT_FLAG_*                               */
+  int64_t lb[NEPTUNE_RT_MAX_RANK], ub[NEPTUNE_RT_MAX_RANK];         /* apply `bounds`       */
+  int64_t out_lb[NEPTUNE_RT_MAX_RANK], out_ub[NEPTUNE_RT_MAX_RANK]; /* result temp bounds   */
+  const int64_t *in_lb;                  /* n_inputs x rank, row-major: input temp bounds   */
+  const int64_t *in_ub;
+} neptune_rt_stencil_desc;
+
+#define NEPTUNE_RT_FLAG_FMA 1            /* allow a*b+c contraction (tolerance tier)        */
+
+typedef struct neptune_rt_ctx neptune_rt_ctx;
+typedef struct neptune_rt_field neptune_rt_field;
+typedef struct neptune_rt_stencil neptune_rt_stencil;
+
+/* ---- context ------------------------------------------------------------------------- */
+/* Replaces the lazy `neptune_rt_init_noargs` (NeptunePETScRuntime.h:47). device < 0 picks
+ * LOCAL_RANK (or 0). */
+int neptune_rt_init(int device, neptune_rt_ctx **ctx);
+int neptune_rt_finalize(neptune_rt_ctx *ctx);
+int neptune_rt_sync(neptune_rt_ctx *ctx);
+/* Message of the last failure on this thread (ctx may be NULL for init failures). */
+const char *neptune_rt_last_error(neptune_rt_ctx *ctx);
+/* Number of kernels this ctx has launched so far (for accounting in benchmarks). */
+int64_t neptune_rt_launch_count(neptune_rt_ctx *ctx);
+/* The CUDA stream sweeps are launched on (a cudaStream_t, returned as void*). */
+void *neptune_rt_stream(neptune_rt_ctx *ctx);
+/* Device-side stopwatch on the sweep stream (CUDA events): start records an event, stop records a
+ * second one, waits for it and returns the elapsed milliseconds between the two. */
+int neptune_rt_timer_start(neptune_rt_ctx *ctx);
+int neptune_rt_timer_stop(neptune_rt_ctx *ctx, double *ms);
+
+/* ---- device fields --------------------------------------------------------------------- */
+/* Storage of a !neptune_ir.field / !temp: identity-layout row-major box `ub - lb`
+ * (NeptuneIRTypeConverter, lib/Passes/DataflowLowering.cpp:41-71), resident in HBM. */
+int neptune_rt_field_alloc(neptune_rt_ctx *ctx, int dtype, int rank, const int64_t *lb,
+                           const int64_t *ub, neptune_rt_field **field);
+int neptune_rt_field_free(neptune_rt_field *field);
+/* Whole-box copies between a contiguous row-major host buffer and the field (async on the ctx
+ * stream; host memory should be pinned for full PCIe speed).  */
+int neptune_rt_field_upload(neptune_rt_field *field, const void *host);
+int neptune_rt_field_download(neptune_rt_field *field, void *host);
+/* Planes [p0, p1) of dim 0 only (used by the pipelined host path and the halo tests). */
+int neptune_rt_field_upload_planes(neptune_rt_field *field, const void *host, int64_t p0, int64_t p1);
+int neptune_rt_field_download_planes(neptune_rt_field *field, void *host, int64_t p0, int64_t p1);
+int neptune_rt_field_fill(neptune_rt_field *field, double value);
+void *neptune_rt_field_device_ptr(neptune_rt_field *field);
+int64_t neptune_rt_field_bytes(neptune_rt_field *field);
+/* `neptune_ir.store` (DataflowLowering.cpp:165-220): whole copy when lb/ub are NULL, else the
+ * sub-box [lb, ub) in logical coordinates of both operands. */
+int neptune_rt_field_store(neptune_rt_field *dst, neptune_rt_field *src, const int64_t *lb,
+                           const int64_t *ub);
+
+/* ---- stencils -------------------------------------------------------------------------- */
+/* 64-bit structure key of a body (constants' values, bounds and extents excluded): two applies
+ * with the same key run the same compiled kernel. Pure host code. */
+uint64_t neptune_rt_body_key(const neptune_rt_stencil_desc *desc);
+/* 1 when the library holds compiled sm_100a kernels for this body key. Pure host code. */
+int neptune_rt_body_compiled(uint64_t key);
+int neptune_rt_stencil_create(neptune_rt_ctx *ctx, const neptune_rt_stencil_desc *desc,
+                              neptune_rt_stencil **stencil);
+int neptune_rt_stencil_destroy(neptune_rt_stencil *stencil);
+/* Tuning knobs, all optional: "variant" = "auto" | "direct" | "tma:<cfg>", "zchunk" = planes
+ * per work item, "tblock" = fused time steps per launch. Unknown keys return EINVAL. */
+int neptune_rt_stencil_set(neptune_rt_stencil *stencil, const char *key, const char *value);
+/* The kernel variants compiled for this stencil's body ("direct", "tma:64x16", ...). */
+int neptune_rt_stencil_variant_count(neptune_rt_stencil *stencil);
+const char *neptune_rt_stencil_variant_name(neptune_rt_stencil *stencil, int index);
+/* Name of the kernel variant the last launch used ("" before the first launch). */
+const char *neptune_rt_stencil_variant(neptune_rt_stencil *stencil);
+/* One sweep, asynchronous on the ctx stream: out = apply(in[0..n_in)). `out` must not alias
+ * an input (the reference allocates a fresh result, DataflowLowering.cpp:273-281). */
+int neptune_rt_apply(neptune_rt_stencil *stencil, int n_in, neptune_rt_field *const *in,
+                     neptune_rt_field *out);
+/* Sweep only planes [p0, p1) of dim 0 of the result box (slab boundary / interior split). */
+int neptune_rt_apply_planes(neptune_rt_stencil *stencil, int n_in, neptune_rt_field *const *in,
+                            neptune_rt_field *out, int64_t p0, int64_t p1, void *stream);
+/* nsteps sweeps ping-ponging a <-> b (in[0] = a on odd steps' input ...): the host time loop of
+ * SURVEY.md §3.3 kept resident on the device. extra[] are inputs 1..n_in-1 (coefficients, rhs).
+ * On return *result is a or b, whichever holds the last state. With a communicator attached
+ * (neptune_rt_comm_init) every step exchanges `halo` ghost planes with the dim-0 neighbours,
+ * overlapped with the interior sweep. */
+int neptune_rt_run_steps(neptune_rt_stencil *stencil, neptune_rt_field *a, neptune_rt_field *b,
+                         int n_extra, neptune_rt_field *const *extra, int64_t nsteps,
+                         neptune_rt_field **result);
+
+/* ---- slab decomposition + halo exchange (dim 0) ----------------------------------------- */
+/* Planes [*begin, *end) of a dim-0 extent n0 owned by `rank` of `nranks` (balanced, contiguous).
+ * Pure host code. */
+int neptune_rt_slab_partition(int64_t n0, int nranks, int rank, int64_t *begin, int64_t *end);
+/* Rewrites a global descriptor into the local one of `rank`: dim-0 bounds of the result and of
+ * every input become [begin - halo, end + halo) clipped to the global box, the apply bounds are
+ * intersected with the owned planes. out_* arrays must hold n_inputs*rank entries. Pure host. */
+int neptune_rt_slab_localize(const neptune_rt_stencil_desc *global_desc, int nranks, int rank,
+                             int64_t halo, neptune_rt_stencil_desc *local_desc,
+                             int64_t *local_in_lb, int64_t *local_in_ub);
+/* 128-byte NCCL unique id (rank 0 creates it; the host harness broadcasts it). */
+int neptune_rt_comm_unique_id(void *id128);
+int neptune_rt_comm_init(neptune_rt_ctx *ctx, const void *id128, int nranks, int rank);
+/* Exchange `width` planes with rank-1 / rank+1: owned boundary planes of `field` go to the
+ * neighbours' ghost planes. own_begin/own_end are the owned planes in field storage rows. */
+int neptune_rt_halo_exchange(neptune_rt_ctx *ctx, neptune_rt_field *field, int64_t own_begin,
+                             int64_t own_end, int64_t width, void *stream);
+
+/* ---- memref-level entry points (what MLIR-generated code calls) -------------------------- */
+/* Host-buffer form of one sweep, the drop-in for the loop nest the reference emits: uploads the
+ * inputs, sweeps, downloads into `out_host`. Buffers are contiguous row-major boxes matching the
+ * descriptor's bounds. Uses a lazily created default ctx and aborts on failure, mirroring
+ * the reference shim's behaviour (NeptunePETScRuntime.cpp:15-30, 91-98). */
+void neptune_rt_apply_memref(const neptune_rt_stencil_desc *desc, int n_in,
+                             const void *const *in_host, void *out_host);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* NEPTUNE_RT_H */

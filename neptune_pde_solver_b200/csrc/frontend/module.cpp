@@ -1,0 +1,489 @@
+// neptune_b200_* — the `neptuneir-to-b200` pipeline as a C ABI (include/neptune_b200.h).
+//
+// Compile time: parse -> ApplyOp::verify rules (parser.cpp) -> recognise every apply
+// (recognizer.cpp) -> plan the runtime calls of each function.  This replaces
+// verify-annotate -> structure-lowering -> dataflow-lowering{backend=cpu}
+// (lib/Pipeline/NeptuneIRPassesPipeline.cpp:10-26) for modules on the apply hot path.
+// Run time: the plan is executed against neptune_rt_* (runtime/runtime.cu); wrap/unwrap/load
+// forward their operand exactly as the reference's lowerings do (DataflowLowering.cpp:131-159),
+// `store` is a device copy (:165-220) unless it is the only use of an apply result, in which
+// case the sweep writes straight into the destination field (the reference's alloc + copy-through
+// + store-copy collapse into the one pass over the data).
+#include <cstdio>
+#include <cstring>
+#include <map>
+#include <set>
+#include <sstream>
+
+#include "ir.h"
+#include "neptune_b200.h"
+
+using namespace neptune;
+
+namespace {
+
+struct ApplyRec {
+  std::string function;
+  StencilDesc desc;
+  std::string cuda_source;
+  const Apply *ap = nullptr;
+};
+
+struct FnInfo {
+  const Function *fn = nullptr;
+  // memref argument -> the field type it is wrapped as (bounds, dtype); index = arg position
+  std::vector<Type> arg_field;        // kind == None when the argument is never wrapped
+  std::vector<bool> arg_needs_upload;
+  std::vector<bool> arg_written;
+  std::map<int, int> fused_store;     // op index of an apply -> op index of the store fused into it
+  std::set<int> elided;               // store ops that became no-ops
+  std::string plan;
+};
+
+}  // namespace
+
+struct neptune_b200_module {
+  Module mod;
+  bool fma = false;
+  std::vector<ApplyRec> applies;
+  std::map<const Apply *, int> apply_index;
+  std::map<std::string, FnInfo> fns;
+  // run-time state, per ctx
+  struct PerCtx {
+    std::vector<neptune_rt_stencil *> stencils;
+    std::map<std::string, std::vector<neptune_rt_field *>> arg_fields;  // function -> device fields of its memref args
+    std::map<int, std::vector<neptune_rt_field *>> temps;               // apply index -> reusable result temps
+    std::map<int, int> cursor;                                          // temps of that apply taken in this run
+  };
+  std::map<neptune_rt_ctx *, PerCtx> per_ctx;
+  std::string err;
+};
+
+namespace {
+
+std::string bounds_str(const Bounds &b) {
+  std::ostringstream o;
+  o << "[";
+  for (int d = 0; d < b.rank(); ++d) o << (d ? "," : "") << b.lb[d];
+  o << "]..[";
+  for (int d = 0; d < b.rank(); ++d) o << (d ? "," : "") << b.ub[d];
+  o << "]";
+  return o.str();
+}
+
+// Resolve a value name to the SSA name of the storage it aliases (wrap/unwrap/load forward).
+std::string root_of(const std::map<std::string, std::string> &alias, std::string v) {
+  for (;;) {
+    auto it = alias.find(v);
+    if (it == alias.end() || it->second == v) return v;
+    v = it->second;
+  }
+}
+
+void analyze_function(neptune_b200_module &m, const Function &fn, FnInfo &fi) {
+  fi.fn = &fn;
+  fi.arg_field.assign(fn.args.size(), Type());
+  fi.arg_needs_upload.assign(fn.args.size(), false);
+  fi.arg_written.assign(fn.args.size(), false);
+  std::map<std::string, int> argpos;
+  for (size_t i = 0; i < fn.args.size(); ++i) argpos[fn.args[i].first] = (int)i;
+  std::map<std::string, std::string> alias;  // value -> value it forwards
+  std::map<std::string, Type> vtype;
+  for (auto &a : fn.args) vtype[a.first] = a.second;
+
+  // uses of every apply result
+  std::map<std::string, std::vector<int>> uses;
+  for (size_t i = 0; i < fn.ops.size(); ++i)
+    for (auto &o : fn.ops[i].operands) uses[o].push_back((int)i);
+
+  std::set<std::string> touched;  // storage roots already read or written
+  std::ostringstream plan;
+  plan << fn.name << ":\n";
+  for (size_t i = 0; i < fn.ops.size(); ++i) {
+    const HostOp &op = fn.ops[i];
+    switch (op.kind) {
+      case HostOp::Wrap: {
+        auto it = argpos.find(op.operands[0]);
+        if (op.types[1].kind != Type::Grid) throw Diagnostic("line " + std::to_string(op.line) + ": wrap must produce a !neptune_ir.field");
+        if (op.types[0].kind != Type::MemRef) throw Diagnostic("line " + std::to_string(op.line) + ": wrap operand must be a memref");
+        if (it != argpos.end()) {
+          Type &t = fi.arg_field[it->second];
+          if (t.kind != Type::None && t != op.types[1])
+            throw Diagnostic("line " + std::to_string(op.line) + ": memref argument wrapped with two different field types", true);
+          t = op.types[1];
+        }
+        alias[op.results[0]] = op.operands[0];
+        vtype[op.results[0]] = op.types[1];
+        plan << "  " << op.results[0] << " = wrap " << op.operands[0] << "  -> neptune_rt_field_alloc(" << (op.types[1].dtype == NEPTUNE_RT_F64 ? "f64" : "f32")
+             << ", " << bounds_str(op.types[1].bounds) << ")\n";
+        break;
+      }
+      case HostOp::Unwrap:
+      case HostOp::Load:
+        alias[op.results[0]] = op.operands[0];
+        vtype[op.results[0]] = op.types[1];
+        plan << "  " << op.results[0] << " = " << (op.kind == HostOp::Load ? "load " : "unwrap ") << op.operands[0] << "  -> forwarded\n";
+        break;
+      case HostOp::ApplyOp: {
+        const Apply &ap = *op.apply;
+        const int idx = m.apply_index.at(&ap);
+        std::set<std::string> in_roots;
+        for (auto &v : ap.inputs) {
+          std::string r = root_of(alias, v);
+          in_roots.insert(r);
+          if (argpos.count(r) && !touched.count(r)) fi.arg_needs_upload[argpos[r]] = true;
+          touched.insert(r);
+        }
+        vtype[op.results[0]] = ap.out_type;
+        // fuse `store %r to %f` when it is the only use of %r, copies the whole box, the field has the
+        // temp's bounds and is not one of the apply's inputs
+        auto &us = uses[op.results[0]];
+        bool fused = false;
+        if (us.size() == 1) {
+          const HostOp &st = fn.ops[us[0]];
+          if (st.kind == HostOp::Store && !st.has_bounds && st.operands[0] == op.results[0]) {
+            std::string droot = root_of(alias, st.operands[1]);
+            bool clobbered = false;  // nothing between the apply and the store may touch the destination
+            for (int j = (int)i + 1; j < us[0]; ++j)
+              for (auto &o : fn.ops[j].operands) clobbered |= root_of(alias, o) == droot;
+            const Type &dt = vtype[st.operands[1]];
+            if (!in_roots.count(droot) && !clobbered && dt.kind == Type::Grid && dt.bounds == ap.out_type.bounds && dt.dtype == ap.out_type.dtype) {
+              fi.fused_store[(int)i] = us[0];
+              fi.elided.insert(us[0]);
+              fused = true;
+              if (argpos.count(droot)) fi.arg_written[argpos[droot]] = true;
+              touched.insert(droot);
+            }
+          }
+        }
+        char key[32];
+        std::snprintf(key, sizeof key, "0x%016llx", (unsigned long long)body_key(m.applies[idx].desc.c));
+        plan << "  " << op.results[0] << " = neptune_rt_apply(stencil #" << idx << " key " << key << ", in = [";
+        for (size_t k = 0; k < ap.inputs.size(); ++k) plan << (k ? ", " : "") << ap.inputs[k];
+        plan << "], bounds = " << bounds_str(ap.bounds) << ")";
+        if (fused) plan << "  -> writes " << fn.ops[us[0]].operands[1] << " directly (store fused)";
+        else plan << "  -> neptune_rt_field_alloc(temp)";
+        plan << "\n";
+        break;
+      }
+      case HostOp::ApplyLinear: {
+        const Function *callee = m.mod.find(op.callee);
+        if (!callee) throw Diagnostic("line " + std::to_string(op.line) + ": call to undefined operator " + op.callee);
+        if (callee->args.size() != op.operands.size()) throw Diagnostic("line " + std::to_string(op.line) + ": operand count differs from " + op.callee);
+        for (auto &v : op.operands) {
+          std::string r = root_of(alias, v);
+          if (argpos.count(r) && !touched.count(r)) fi.arg_needs_upload[argpos[r]] = true;
+          touched.insert(r);
+        }
+        vtype[op.results[0]] = op.types.back();
+        plan << "  " << op.results[0] << " = call " << op.callee << "(...)\n";
+        break;
+      }
+      case HostOp::Store: {
+        std::string sroot = root_of(alias, op.operands[0]), droot = root_of(alias, op.operands[1]);
+        if (fi.elided.count((int)i)) {
+          plan << "  store " << op.operands[0] << " to " << op.operands[1] << "  -> elided (fused into the apply)\n";
+          break;
+        }
+        if (argpos.count(sroot) && !touched.count(sroot)) fi.arg_needs_upload[argpos[sroot]] = true;
+        touched.insert(sroot);
+        if (argpos.count(droot)) {
+          // a partial store leaves the rest of the destination visible: it must be uploaded first
+          if (op.has_bounds && !touched.count(droot)) fi.arg_needs_upload[argpos[droot]] = true;
+          fi.arg_written[argpos[droot]] = true;
+        }
+        touched.insert(droot);
+        plan << "  store " << op.operands[0] << " to " << op.operands[1] << "  -> neptune_rt_field_store("
+             << (op.has_bounds ? bounds_str(op.bounds) : std::string("whole")) << ")\n";
+        break;
+      }
+      case HostOp::Return:
+        plan << "  return";
+        for (auto &v : op.operands) plan << " " << v;
+        plan << "\n";
+        break;
+      case HostOp::Constant: break;
+    }
+  }
+  for (size_t i = 0; i < fn.args.size(); ++i)
+    if (fi.arg_field[i].kind == Type::Grid)
+      plan << "  arg " << i << " " << fn.args[i].first << ": " << (fi.arg_needs_upload[i] ? "upload" : "no upload")
+           << ", " << (fi.arg_written[i] ? "download" : "no download") << "\n";
+  fi.plan = plan.str();
+}
+
+struct Exec {
+  neptune_b200_module &m;
+  neptune_rt_ctx *ctx;
+  neptune_b200_module::PerCtx &pc;
+  std::vector<neptune_rt_field *> scratch;  // temps of opdef calls, freed by the caller of run()
+
+  int fail(int code, const std::string &msg) {
+    m.err = msg;
+    return code;
+  }
+  int rt_fail(int code) {
+    m.err = neptune_rt_last_error(ctx);
+    return code;
+  }
+
+  neptune_rt_stencil *stencil(int idx, int *rc) {
+    if ((int)pc.stencils.size() < (int)m.applies.size()) pc.stencils.resize(m.applies.size(), nullptr);
+    if (!pc.stencils[idx]) {
+      *rc = neptune_rt_stencil_create(ctx, &m.applies[idx].desc.c, &pc.stencils[idx]);
+      if (*rc) { rt_fail(*rc); return nullptr; }
+    }
+    return pc.stencils[idx];
+  }
+
+  // Execute `fn` with its arguments bound to device fields; *ret receives the returned value's field.
+  int run(const Function &fn, const std::vector<neptune_rt_field *> &args, neptune_rt_field **ret) {
+    const FnInfo &fi = m.fns.at(fn.name);
+    std::map<std::string, neptune_rt_field *> env;
+    for (size_t i = 0; i < fn.args.size(); ++i) env[fn.args[i].first] = args[i];
+    for (size_t i = 0; i < fn.ops.size(); ++i) {
+      const HostOp &op = fn.ops[i];
+      switch (op.kind) {
+        case HostOp::Wrap:
+        case HostOp::Unwrap:
+        case HostOp::Load:
+          env[op.results[0]] = env[op.operands[0]];
+          break;
+        case HostOp::ApplyOp: {
+          const Apply &ap = *op.apply;
+          const int idx = m.apply_index.at(&ap);
+          int rc = 0;
+          neptune_rt_stencil *st = stencil(idx, &rc);
+          if (!st) return rc;
+          std::vector<neptune_rt_field *> ins;
+          for (auto &v : ap.inputs) {
+            if (!env.count(v) || !env[v]) return fail(NEPTUNE_RT_EINVAL, "apply input " + v + " has no storage");
+            ins.push_back(env[v]);
+          }
+          neptune_rt_field *out = nullptr;
+          auto fs = fi.fused_store.find((int)i);
+          if (fs != fi.fused_store.end()) {
+            out = env[fn.ops[fs->second].operands[1]];
+          } else {
+            // the n-th execution of this apply within one top-level run owns the n-th pooled temp, so
+            // two live results of the same opdef never share storage
+            auto &pool = pc.temps[idx];
+            int &cur = pc.cursor[idx];
+            if (cur >= (int)pool.size()) {
+              const neptune_rt_stencil_desc &d = m.applies[idx].desc.c;
+              neptune_rt_field *f = nullptr;
+              if ((rc = neptune_rt_field_alloc(ctx, d.dtype, d.rank, d.out_lb, d.out_ub, &f))) return rt_fail(rc);
+              pool.push_back(f);
+            }
+            out = pool[cur++];
+          }
+          if ((rc = neptune_rt_apply(st, (int)ins.size(), ins.data(), out))) return rt_fail(rc);
+          env[op.results[0]] = out;
+          break;
+        }
+        case HostOp::ApplyLinear: {
+          const Function *callee = m.mod.find(op.callee);
+          std::vector<neptune_rt_field *> cargs;
+          for (auto &v : op.operands) cargs.push_back(env[v]);
+          neptune_rt_field *r = nullptr;
+          if (int rc = run(*callee, cargs, &r)) return rc;
+          env[op.results[0]] = r;
+          break;
+        }
+        case HostOp::Store: {
+          if (fi.elided.count((int)i)) break;
+          neptune_rt_field *src = env[op.operands[0]], *dst = env[op.operands[1]];
+          if (!src || !dst) return fail(NEPTUNE_RT_EINVAL, "store operand has no storage");
+          int rc;
+          if (op.has_bounds) rc = neptune_rt_field_store(dst, src, op.bounds.lb.data(), op.bounds.ub.data());
+          else rc = neptune_rt_field_store(dst, src, nullptr, nullptr);
+          if (rc) return rt_fail(rc);
+          break;
+        }
+        case HostOp::Return:
+          if (ret) *ret = op.operands.empty() ? nullptr : env[op.operands[0]];
+          return NEPTUNE_RT_OK;
+        case HostOp::Constant: break;
+      }
+    }
+    if (ret) *ret = nullptr;
+    return NEPTUNE_RT_OK;
+  }
+};
+
+int bind_args(neptune_b200_module &m, neptune_rt_ctx *ctx, const Function &fn, std::vector<neptune_rt_field *> **out) {
+  auto &pc = m.per_ctx[ctx];
+  auto &v = pc.arg_fields[fn.name];
+  const FnInfo &fi = m.fns.at(fn.name);
+  if (v.empty()) {
+    v.assign(fn.args.size(), nullptr);
+    for (size_t i = 0; i < fn.args.size(); ++i) {
+      const Type &t = fi.arg_field[i];
+      if (t.kind != Type::Grid) continue;
+      if (int rc = neptune_rt_field_alloc(ctx, t.dtype, t.bounds.rank(), t.bounds.lb.data(), t.bounds.ub.data(), &v[i])) {
+        m.err = neptune_rt_last_error(ctx);
+        return rc;
+      }
+    }
+  }
+  *out = &v;
+  return NEPTUNE_RT_OK;
+}
+
+}  // namespace
+
+extern "C" int neptune_b200_compile(const char *text, const char *pipeline, neptune_b200_module **out, char *err, size_t err_len) {
+  auto report = [&](const std::string &msg) {
+    if (err && err_len) {
+      std::snprintf(err, err_len, "%s", msg.c_str());
+    }
+  };
+  if (out) *out = nullptr;
+  if (!text || !pipeline || !out) { report("neptune_b200_compile: NULL argument"); return NEPTUNE_RT_EINVAL; }
+  std::string pl = pipeline;
+  bool fma = false;
+  const std::string name = "neptuneir-to-b200";
+  if (pl.compare(0, name.size(), name) != 0) {
+    report("unknown pipeline '" + pl + "' (this library registers 'neptuneir-to-b200'; 'neptuneir-to-llvm' is the reference's CPU pipeline and is not provided here)");
+    return NEPTUNE_RT_EINVAL;
+  }
+  std::string opts = pl.substr(name.size());
+  if (!opts.empty()) {
+    if (opts == "{fma=true}" || opts == "{fma=1}") fma = true;
+    else if (opts == "{fma=false}" || opts == "{fma=0}" || opts == "{}") fma = false;
+    else { report("unknown pipeline options '" + opts + "' (supported: {fma=true|false})"); return NEPTUNE_RT_EINVAL; }
+  }
+  auto *m = new neptune_b200_module();
+  m->fma = fma;
+  try {
+    m->mod = parse_module(text);
+    for (auto &fn : m->mod.functions)
+      for (auto &op : fn.ops)
+        if (op.kind == HostOp::ApplyOp) {
+          ApplyRec r;
+          r.function = fn.name;
+          r.ap = op.apply.get();
+          r.desc = recognize_apply(*op.apply, fma);
+          r.cuda_source = generate_functor(r.desc.c);
+          m->apply_index[op.apply.get()] = (int)m->applies.size();
+          m->applies.push_back(std::move(r));
+        }
+    for (auto &fn : m->mod.functions) analyze_function(*m, fn, m->fns[fn.name]);
+  } catch (const Diagnostic &d) {
+    report(d.what());
+    const int rc = d.unsupported ? NEPTUNE_RT_EUNSUPPORTED : NEPTUNE_RT_EINVAL;
+    delete m;
+    return rc;
+  } catch (const std::exception &e) {
+    report(std::string("internal error: ") + e.what());
+    delete m;
+    return NEPTUNE_RT_EINVAL;
+  }
+  *out = m;
+  return NEPTUNE_RT_OK;
+}
+
+extern "C" int neptune_b200_module_destroy(neptune_b200_module *m) {
+  if (!m) return NEPTUNE_RT_OK;
+  for (auto &pc : m->per_ctx) {
+    for (auto *s : pc.second.stencils) neptune_rt_stencil_destroy(s);
+    for (auto &kv : pc.second.arg_fields)
+      for (auto *f : kv.second) neptune_rt_field_free(f);
+    for (auto &kv : pc.second.temps)
+      for (auto *f : kv.second) neptune_rt_field_free(f);
+  }
+  delete m;
+  return NEPTUNE_RT_OK;
+}
+
+extern "C" int neptune_b200_apply_count(neptune_b200_module *m) { return m ? (int)m->applies.size() : 0; }
+extern "C" const neptune_rt_stencil_desc *neptune_b200_apply_desc(neptune_b200_module *m, int i) {
+  return (m && i >= 0 && i < (int)m->applies.size()) ? &m->applies[i].desc.c : nullptr;
+}
+extern "C" const char *neptune_b200_apply_function(neptune_b200_module *m, int i) {
+  return (m && i >= 0 && i < (int)m->applies.size()) ? m->applies[i].function.c_str() : nullptr;
+}
+extern "C" const char *neptune_b200_apply_cuda_source(neptune_b200_module *m, int i) {
+  return (m && i >= 0 && i < (int)m->applies.size()) ? m->applies[i].cuda_source.c_str() : nullptr;
+}
+extern "C" const char *neptune_b200_function_plan(neptune_b200_module *m, const char *fn) {
+  if (!m || !fn) return nullptr;
+  auto it = m->fns.find(fn);
+  return it == m->fns.end() ? nullptr : it->second.plan.c_str();
+}
+extern "C" int neptune_b200_function_arg_count(neptune_b200_module *m, const char *fn) {
+  if (!m || !fn) return -1;
+  const Function *f = m->mod.find(fn);
+  return f ? (int)f->args.size() : -1;
+}
+extern "C" int64_t neptune_b200_function_arg_numel(neptune_b200_module *m, const char *fn, int arg) {
+  if (!m || !fn) return -1;
+  auto it = m->fns.find(fn);
+  if (it == m->fns.end() || arg < 0 || arg >= (int)it->second.arg_field.size()) return -1;
+  const Type &t = it->second.arg_field[arg];
+  return t.kind == Type::Grid ? t.bounds.numel() : -1;
+}
+extern "C" const char *neptune_b200_last_error(neptune_b200_module *m) { return m ? m->err.c_str() : ""; }
+
+extern "C" neptune_rt_stencil *neptune_b200_apply_stencil(neptune_b200_module *m, neptune_rt_ctx *ctx, int index) {
+  if (!m || !ctx || index < 0 || index >= (int)m->applies.size()) return nullptr;
+  Exec ex{*m, ctx, m->per_ctx[ctx], {}};
+  int rc = 0;
+  return ex.stencil(index, &rc);
+}
+
+extern "C" int neptune_b200_run_host(neptune_b200_module *m, neptune_rt_ctx *ctx, const char *function, int n_args, void *const *args) {
+  if (!m || !ctx || !function || (n_args > 0 && !args)) return NEPTUNE_RT_EINVAL;
+  const Function *fn = m->mod.find(function);
+  if (!fn) { m->err = std::string("no function ") + function; return NEPTUNE_RT_EINVAL; }
+  if (fn->kind != "func") { m->err = "only func.func entries can be run from host buffers"; return NEPTUNE_RT_EINVAL; }
+  if ((int)fn->args.size() != n_args) { m->err = "argument count mismatch"; return NEPTUNE_RT_EINVAL; }
+  const FnInfo &fi = m->fns.at(fn->name);
+  std::vector<neptune_rt_field *> *fields = nullptr;
+  if (int rc = bind_args(*m, ctx, *fn, &fields)) return rc;
+  for (int i = 0; i < n_args; ++i)
+    if ((*fields)[i] && fi.arg_needs_upload[i])
+      if (int rc = neptune_rt_field_upload((*fields)[i], args[i])) { m->err = neptune_rt_last_error(ctx); return rc; }
+  Exec ex{*m, ctx, m->per_ctx[ctx], {}};
+  ex.pc.cursor.clear();
+  if (int rc = ex.run(*fn, *fields, nullptr)) return rc;
+  for (int i = 0; i < n_args; ++i)
+    if ((*fields)[i] && fi.arg_written[i])
+      if (int rc = neptune_rt_field_download((*fields)[i], args[i])) { m->err = neptune_rt_last_error(ctx); return rc; }
+  if (int rc = neptune_rt_sync(ctx)) { m->err = neptune_rt_last_error(ctx); return rc; }
+  return NEPTUNE_RT_OK;
+}
+
+extern "C" int neptune_b200_run_steps_host(neptune_b200_module *m, neptune_rt_ctx *ctx, const char *function, int n_args,
+                                           void *const *args, int64_t nsteps, int *result_arg) {
+  if (!m || !ctx || !function || n_args < 2 || !args || nsteps < 0) return NEPTUNE_RT_EINVAL;
+  const Function *fn = m->mod.find(function);
+  if (!fn) { m->err = std::string("no function ") + function; return NEPTUNE_RT_EINVAL; }
+  if (fn->kind != "func" || (int)fn->args.size() != n_args) { m->err = "argument count mismatch"; return NEPTUNE_RT_EINVAL; }
+  const FnInfo &fi = m->fns.at(fn->name);
+  std::vector<neptune_rt_field *> *fields = nullptr;
+  if (int rc = bind_args(*m, ctx, *fn, &fields)) return rc;
+  if (!(*fields)[0] || !(*fields)[1] || fi.arg_field[0] != fi.arg_field[1]) {
+    m->err = "run_steps needs entry(out, in, ...) with out and in wrapped as the same field type";
+    return NEPTUNE_RT_EINVAL;
+  }
+  // the swapped host loop reads both buffers over time: upload every argument the entry reads,
+  // and arg 0 too when the entry reads it before overwriting it
+  for (int i = 0; i < n_args; ++i)
+    if ((*fields)[i] && (fi.arg_needs_upload[i] || (i == 1 && fi.arg_needs_upload[0])))
+      if (int rc = neptune_rt_field_upload((*fields)[i], args[i])) { m->err = neptune_rt_last_error(ctx); return rc; }
+  Exec ex{*m, ctx, m->per_ctx[ctx], {}};
+  std::vector<neptune_rt_field *> cur = *fields;
+  for (int64_t t = 0; t < nsteps; ++t) {
+    ex.pc.cursor.clear();
+    if (int rc = ex.run(*fn, cur, nullptr)) return rc;
+    std::swap(cur[0], cur[1]);
+  }
+  // step t writes host argument (t even ? 0 : 1)
+  const int res = nsteps == 0 ? 1 : ((nsteps - 1) % 2 == 0 ? 0 : 1);
+  if (nsteps > 0)
+    if (int rc = neptune_rt_field_download((*fields)[res], args[res])) { m->err = neptune_rt_last_error(ctx); return rc; }
+  if (result_arg) *result_arg = res;
+  if (int rc = neptune_rt_sync(ctx)) { m->err = neptune_rt_last_error(ctx); return rc; }
+  return NEPTUNE_RT_OK;
+}

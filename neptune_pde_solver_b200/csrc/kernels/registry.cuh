@@ -1,0 +1,156 @@
+// Launchers + registration of the sweep kernels for one body functor.
+// Included only by the generated units (build/gen/body_*.cu).
+#pragma once
+#include <algorithm>
+
+#include "registry.h"
+#include "sweep_direct.cuh"
+#include "sweep_tma.cuh"
+
+namespace neptune {
+
+template <class F> void fill_params(KParams<F> &p, const SweepArgs &a) {
+  typedef typename F::T T;
+  p.out = static_cast<T *>(a.out);
+  p.copy_src = static_cast<const T *>(a.copy_src);
+  for (int k = 0; k < F::NIN; ++k) {
+    p.in[k] = static_cast<const T *>(a.in[k]);
+    p.in_sz[k] = a.in_sz[k];
+    p.in_sy[k] = a.in_sy[k];
+  }
+  p.out_sz = a.out_sz; p.out_sy = a.out_sy;
+  p.nz = a.nz; p.ny = a.ny; p.nx = a.nx;
+  for (int d = 0; d < 3; ++d) { p.blo[d] = a.blo[d]; p.bhi[d] = a.bhi[d]; p.wlo[d] = a.wlo[d]; p.whi[d] = a.whi[d]; }
+  p.zchunk = p.nchunks = p.ncx = p.ncy = p.cxo = p.cyo = p.nitems = 0;
+  for (int i = 0; i < F::NCONST; ++i) p.c[i] = (T)a.consts[i];
+  if (F::NCONST == 0) p.c[0] = T(0);
+}
+
+template <class F, bool FMA> int launch_direct(const SweepArgs &a) {
+  KParams<F> p;
+  fill_params<F>(p, a);
+  const int wx = a.whi[2] - a.wlo[2], wy = a.whi[1] - a.wlo[1], wz = a.whi[0] - a.wlo[0];
+  if (wx <= 0 || wy <= 0 || wz <= 0) return 0;
+  dim3 grid((wx + DIRECT_BX - 1) / DIRECT_BX, (wy + DIRECT_BY - 1) / DIRECT_BY, wz);
+  if (grid.y > 65535u || grid.z > 65535u) return (int)cudaErrorInvalidConfiguration;
+  sweep_direct<F, FMA><<<grid, dim3(DIRECT_BX, DIRECT_BY, 1), 0, a.stream>>>(p);
+  return (int)cudaGetLastError();
+}
+
+// planes per work item: balance the persistent grid against the z-halo re-read per chunk
+inline int choose_zchunk(int planes, int ncols, int grid_slots, int rz) {
+  if (rz == 0 || planes <= 1) return std::max(planes, 1);
+  const int cand[] = {24, 32, 48, 64, 96, 128, 192, 256, planes};
+  double best = -1;
+  int best_zc = planes;
+  for (int zc : cand) {
+    if (zc > planes) zc = planes;
+    const long long chunks = (planes + zc - 1) / zc;
+    const long long items = chunks * ncols;
+    const long long rounds = (items + grid_slots - 1) / grid_slots;
+    const double balance = (double)items / (double)(rounds * std::min<long long>(grid_slots, items));
+    const double halo = (double)zc / (double)(zc + 2 * rz);
+    const double score = balance * halo;
+    if (score > best + 1e-9) { best = score; best_zc = zc; }
+  }
+  return best_zc;
+}
+
+template <class F, class C, bool FMA> int launch_tma(const SweepArgs &a) {
+  typedef TmaGeom<F, C> G;
+  auto kernel = sweep_tma<F, C, FMA>;
+  static int occ_cached[16] = {0};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (dev < 0 || dev >= 16) dev = 0;
+  if (occ_cached[dev] == 0) {
+    cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, G::SMEM_BYTES);
+    if (e != cudaSuccess) return (int)e;
+    int occ = 0;
+    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kernel, G::THREADS, G::SMEM_BYTES);
+    if (e != cudaSuccess) return (int)e;
+    if (occ < 1) return (int)cudaErrorLaunchOutOfResources;
+    occ_cached[dev] = occ;
+  }
+  if (!a.tmap) return (int)cudaErrorInvalidValue;
+  KParams<F> p;
+  fill_params<F>(p, a);
+  const int wz = a.whi[0] - a.wlo[0];
+  if (wz <= 0 || a.whi[1] <= a.wlo[1] || a.whi[2] <= a.wlo[2]) return 0;
+  p.cxo = a.wlo[2] / C::TX;
+  p.cyo = a.wlo[1] / C::TY;
+  p.ncx = (a.whi[2] + C::TX - 1) / C::TX - p.cxo;
+  p.ncy = (a.whi[1] + C::TY - 1) / C::TY - p.cyo;
+  const int ncols = p.ncx * p.ncy;
+  const int slots = a.sm_count * occ_cached[dev];
+  p.zchunk = a.zchunk > 0 ? std::min(a.zchunk, wz) : choose_zchunk(wz, ncols, slots, F::RZ);
+  p.nchunks = (wz + p.zchunk - 1) / p.zchunk;
+  const long long items = (long long)p.nchunks * ncols;
+  if (items > 0x7fffffffLL) return (int)cudaErrorInvalidConfiguration;
+  p.nitems = (int)items;
+  const int grid = (int)std::min<long long>(items, slots);
+  kernel<<<grid, G::THREADS, G::SMEM_BYTES, a.stream>>>(p, *a.tmap);
+  return (int)cudaGetLastError();
+}
+
+template <class F, class C, bool FMA> Variant tma_variant(const char *name) {
+  typedef TmaGeom<F, C> G;
+  Variant v;
+  v.name = name;
+  v.kind = VARIANT_TMA;
+  v.fma = FMA;
+  v.tx = C::TX; v.ty = C::TY;
+  v.box_x = G::SXP; v.box_y = G::SY;
+  v.halo_x = G::HX; v.halo_y = G::RY;
+  v.threads = G::THREADS; v.smem = G::SMEM_BYTES;
+  v.launch = &launch_tma<F, C, FMA>;
+  return v;
+}
+
+// tile menus (elements).  3-D bodies march in z; bodies without z taps (2-D) take bigger tiles.
+typedef TileCfg<64, 16, 2, 6, 2> Tile3A;
+typedef TileCfg<128, 8, 2, 6, 2> Tile3B;
+typedef TileCfg<128, 16, 4, 5, 2> Tile3C;
+typedef TileCfg<64, 32, 4, 5, 2> Tile3D;
+typedef TileCfg<64, 8, 1, 6, 1> Tile3W;   // many-input bodies (one coefficient field per tap)
+typedef TileCfg<128, 32, 8, 3, 2> Tile2A;
+typedef TileCfg<128, 16, 4, 4, 2> Tile2B;
+typedef TileCfg<64, 64, 8, 3, 2> Tile2C;
+
+template <class F> struct BodyRegistrar {
+  BodyRegistrar() {
+    BodyEntry e;
+    e.key = F::KEY; e.rank = F::RANK; e.dtype = sizeof(typename F::T) == 8 ? NEPTUNE_RT_F64 : NEPTUNE_RT_F32;
+    e.nin = F::NIN; e.nconst = F::NCONST; e.staged = F::STAGED;
+    e.rz = F::RZ; e.ry = F::RY; e.rx = F::RX; e.ntaps = F::NTAPS; e.flops = F::FLOPS;
+    Variant d;
+    d.name = "direct"; d.kind = VARIANT_DIRECT; d.fma = false; d.threads = DIRECT_BX * DIRECT_BY;
+    d.launch = &launch_direct<F, false>;
+    e.variants.push_back(d);
+    d.fma = true; d.launch = &launch_direct<F, true>;
+    e.variants.push_back(d);
+    // the staged kernel copies through the staged centre value, so it needs input 0 staged
+    if constexpr (F::STAGED == 0 && F::RANK >= 2 && F::RZ <= 1 && F::RY <= 1 && F::RX <= 1) {
+      if constexpr (F::NIN > 4) {
+        e.variants.push_back(tma_variant<F, Tile3W, false>("tma:64x8"));
+        e.variants.push_back(tma_variant<F, Tile3W, true>("tma:64x8"));
+      } else if constexpr (F::RZ > 0) {
+        e.variants.push_back(tma_variant<F, Tile3A, false>("tma:64x16"));
+        e.variants.push_back(tma_variant<F, Tile3A, true>("tma:64x16"));
+        e.variants.push_back(tma_variant<F, Tile3B, false>("tma:128x8"));
+        e.variants.push_back(tma_variant<F, Tile3C, false>("tma:128x16"));
+        e.variants.push_back(tma_variant<F, Tile3D, false>("tma:64x32"));
+      } else {
+        e.variants.push_back(tma_variant<F, Tile2A, false>("tma:128x32"));
+        e.variants.push_back(tma_variant<F, Tile2A, true>("tma:128x32"));
+        e.variants.push_back(tma_variant<F, Tile2B, false>("tma:128x16"));
+        e.variants.push_back(tma_variant<F, Tile2C, false>("tma:64x64"));
+      }
+    }
+    register_body(std::move(e));
+  }
+};
+
+}  // namespace neptune
+
+#define NEPTUNE_REGISTER_BODY(F) static neptune::BodyRegistrar<F> neptune_registrar_##F;

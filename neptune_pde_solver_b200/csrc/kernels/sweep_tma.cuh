@@ -1,0 +1,275 @@
+// TMA-staged persistent sweep kernel for sm_100a (the fast path of `neptune_ir.apply`).
+//
+// Data movement
+//   * the one input that is read at neighbour offsets (the "staged" input) is brought into shared
+//     memory by the Tensor Memory Accelerator: one cp.async.bulk.tensor.3d per plane-tile, a box of
+//     (TX + 2*HX) x (TY + 2*RY) x 1 elements including its x/y halo, completion signalled on an
+//     mbarrier (no thread ever issues a global load for it, out-of-box halo elements are
+//     zero-filled by the TMA unit and never feed an in-bounds point);
+//   * a ring of NS such stages lets the TMA unit run NS - 2*RZ - 1 planes ahead of the math, which
+//     is what keeps enough bytes in flight to cover HBM latency at ~6.5 TB/s;
+//   * inputs read only at offset 0 (coefficient fields, right-hand sides) stream straight from
+//     global memory with 128-bit read-only loads; results leave with 128-bit stores.
+// Work decomposition
+//   * the result box is cut into columns of TY x TX points; a column is cut into chunks of
+//     `zchunk` planes; work item = (chunk, column), chunk-major, so that all columns of a chunk
+//     are swept in lockstep by neighbouring CTAs and their shared halos are L2 hits;
+//   * the grid is persistent: CTA b takes items b, b + gridDim.x, ...; its plane loads form ONE
+//     continuous stream, so the ring never drains between items;
+//   * every thread owns VY x VX points of the tile (VX * sizeof(T) = 16 bytes) and evaluates the
+//     body functor on a register window read from the ring with 128-bit LDS.
+// Semantics = ApplyToSCFForLowering (lib/Passes/DataflowLowering.cpp:258-448): out = copy of
+// input 0, then body over `bounds`; here both in one pass (points outside `bounds` store the
+// staged centre value, which IS input 0 — the host only selects this kernel when input 0 is the
+// staged input).
+#pragma once
+#include <cuda.h>
+
+#include "common.cuh"
+
+namespace neptune {
+
+template <int TX_, int TY_, int VY_, int NS_, int MINB_> struct TileCfg {
+  static constexpr int TX = TX_, TY = TY_, VY = VY_, NS = NS_, MINB = MINB_;
+};
+
+template <class F, class C> struct TmaGeom {
+  typedef typename F::T T;
+  static constexpr int S = sizeof(T);
+  static constexpr int VX = 16 / S;
+  static constexpr int RZ = F::RZ, RY = F::RY, RX = F::RX;
+  static constexpr int HX = RX > 0 ? ((RX + VX - 1) / VX) * VX : 0;  // x halo, kept 16-byte aligned
+  static constexpr int SXP = C::TX + 2 * HX;                        // stage row pitch (elements)
+  static constexpr int SY = C::TY + 2 * RY;                         // stage rows
+  static constexpr int STAGE_TX_BYTES = SXP * SY * S;               // bytes one TMA box delivers
+  static constexpr int STAGE_BYTES = (STAGE_TX_BYTES + 127) / 128 * 128;
+  static constexpr int NTX = C::TX / VX, NTY = C::TY / C::VY;
+  static constexpr int THREADS = NTX * NTY;
+  static constexpr int NS = C::NS;
+  static constexpr int SMEM_BYTES = NS * STAGE_BYTES + NS * 8 + 128;  // + barriers + alignment slack
+  static_assert(NS >= 2 * RZ + 2, "ring must hold the z window plus one plane in flight");
+  static_assert(C::TX % VX == 0 && C::TY % C::VY == 0, "tile must be a multiple of the thread tile");
+  static_assert(SXP <= 256 && SY <= 256, "TMA box dimensions are limited to 256 elements");
+  static_assert(THREADS % 32 == 0 && THREADS <= 1024, "bad thread count");
+};
+
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+  uint32_t done;
+  int spins = 0;
+  do {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(done)
+        : "r"(bar), "r"(parity)
+        : "memory");
+    if (!done && ++spins > (1 << 22)) __trap();  // a lost TMA completion must fail loudly, never hang the GPU
+  } while (!done);
+}
+__device__ __forceinline__ void tma_load_3d(uint32_t dst, const CUtensorMap *map, int x, int y, int z, uint32_t bar) {
+  asm volatile(
+      "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];"
+      ::"r"(dst), "l"((uint64_t)map), "r"(x), "r"(y), "r"(z), "r"(bar)
+      : "memory");
+}
+
+template <class T> struct Vec16;
+template <> struct Vec16<double> { typedef double2 type; };
+template <> struct Vec16<float> { typedef float4 type; };
+
+template <class T, int VX> __device__ __forceinline__ void lds_vec(T (&dst)[VX], const T *src) {
+  typedef typename Vec16<T>::type V;
+  union { V v; T e[VX]; } u;
+  u.v = *reinterpret_cast<const V *>(src);
+#pragma unroll
+  for (int i = 0; i < VX; ++i) dst[i] = u.e[i];
+}
+template <class T, int VX> __device__ __forceinline__ void ldg_vec(T (&dst)[VX], const T *src) {
+  typedef typename Vec16<T>::type V;
+  union { V v; T e[VX]; } u;
+  u.v = __ldg(reinterpret_cast<const V *>(src));
+#pragma unroll
+  for (int i = 0; i < VX; ++i) dst[i] = u.e[i];
+}
+template <class T, int VX> __device__ __forceinline__ void stg_vec(T *dst, const T (&src)[VX]) {
+  typedef typename Vec16<T>::type V;
+  union { V v; T e[VX]; } u;
+#pragma unroll
+  for (int i = 0; i < VX; ++i) u.e[i] = src[i];
+  *reinterpret_cast<V *>(dst) = u.v;
+}
+
+// register window accessor for thread-tile point (IY, IX)
+template <class F, class G, int VY, int IY, int IX> struct WinAcc {
+  typedef typename F::T T;
+  static constexpr int NPW = F::NIN > 1 ? F::NIN - 1 : 1;
+  const T (&w)[2 * G::RZ + 1][VY + 2 * G::RY][G::VX + 2 * G::RX];
+  const T (&pw)[NPW][VY][G::VX];
+  template <int K, int DZ, int DY, int DX> __device__ __forceinline__ T tap() const {
+    if constexpr (K == F::STAGED) {
+      return w[DZ + G::RZ][IY + DY + G::RY][IX + DX + G::RX];
+    } else {
+      static_assert(DZ == 0 && DY == 0 && DX == 0, "non-staged inputs are read at offset 0 only");
+      return pw[K < F::STAGED ? K : K - 1][IY][IX];
+    }
+  }
+};
+
+template <class F, class C, bool FMA>
+__global__ void __launch_bounds__((TmaGeom<F, C>::THREADS), C::MINB)
+sweep_tma(const __grid_constant__ KParams<F> p, const __grid_constant__ CUtensorMap tmap) {
+  typedef TmaGeom<F, C> G;
+  typedef typename F::T T;
+  constexpr int RZ = G::RZ, RY = G::RY, RX = G::RX, HX = G::HX, VX = G::VX, VY = C::VY, NS = G::NS;
+  constexpr int NPW = F::NIN > 1 ? F::NIN - 1 : 1;
+
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  unsigned char *smem = reinterpret_cast<unsigned char *>((reinterpret_cast<uintptr_t>(smem_raw) + 127) & ~uintptr_t(127));
+  const uint32_t bar0 = smem_u32(smem + NS * G::STAGE_BYTES);
+  const uint32_t stage0 = smem_u32(smem);
+
+  const int tid = threadIdx.x;
+  const int tx = tid % G::NTX, ty = tid / G::NTX;
+  const int lx = tx * VX, ly = ty * VY;  // tile-local origin of this thread's points
+
+  if (tid == 0) {
+    for (int s = 0; s < NS; ++s) mbar_init(bar0 + 8 * s, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
+
+  // work item -> geometry
+  auto geom = [&](int item, int &zb, int &ze, int &y0, int &x0) {
+    const int ncols = p.ncx * p.ncy;
+    const int chunk = item / ncols, col = item - chunk * ncols;
+    const int cx = col / p.ncy, cy = col - cx * p.ncy;
+    zb = p.wlo[0] + chunk * p.zchunk;
+    ze = min(p.whi[0], zb + p.zchunk);
+    y0 = (p.cyo + cy) * C::TY;
+    x0 = (p.cxo + cx) * C::TX;
+  };
+
+  // ---- producer: thread 0 streams plane-tiles into the ring ----------------------------------
+  int p_item = blockIdx.x, p_j = 0;
+  unsigned p_count = 0;
+  auto issue = [&]() {
+    if (p_item >= p.nitems) return;
+    int zb, ze, y0, x0;
+    geom(p_item, zb, ze, y0, x0);
+    const unsigned s = p_count % NS;
+    mbar_expect_tx(bar0 + 8 * s, G::STAGE_TX_BYTES);
+    tma_load_3d(stage0 + s * G::STAGE_BYTES, &tmap, x0 - HX, y0 - RY, zb - RZ + p_j, bar0 + 8 * s);
+    ++p_count;
+    if (++p_j == ze - zb + 2 * RZ) { p_j = 0; p_item += gridDim.x; }
+  };
+  if (tid == 0) {
+    for (int s = 0; s < NS; ++s) issue();
+  }
+
+  // ---- consumers --------------------------------------------------------------------------------
+  unsigned n = 0;  // slots consumed so far
+  for (int item = blockIdx.x; item < p.nitems; item += gridDim.x) {
+    int zb, ze, y0, x0;
+    geom(item, zb, ze, y0, x0);
+    const int gx = x0 + lx, gy = y0 + ly;
+    const bool live = gx < p.whi[2] && gy < p.whi[1] && gx + VX > p.wlo[2] && gy + VY > p.wlo[1];
+    const int nslots = ze - zb + 2 * RZ;
+    for (int j = 0; j < nslots; ++j, ++n) {
+      const bool compute = j >= 2 * RZ;
+      const int z = zb + j - 2 * RZ;
+
+      // pointwise inputs: 128-bit streaming loads, issued before the wait so they overlap it
+      T pw[NPW][VY][VX];
+      if constexpr (F::NIN > 1) {
+        if (compute && live) {
+          static_for<F::NIN>([&](auto kc) {
+            constexpr int K = decltype(kc)::value;
+            if constexpr (K != F::STAGED) {
+              constexpr int PK = K < F::STAGED ? K : K - 1;
+#pragma unroll
+              for (int iy = 0; iy < VY; ++iy) {
+                if (gy + iy < p.ny) {
+                  const T *src = p.in[K] + (long long)z * p.in_sz[K] + (long long)(gy + iy) * p.in_sy[K] + gx;
+                  if (gx + VX <= p.nx) {
+                    ldg_vec<T, VX>(pw[PK][iy], src);
+                  } else {
+#pragma unroll
+                    for (int ix = 0; ix < VX; ++ix) pw[PK][iy][ix] = (gx + ix < p.nx) ? __ldg(src + ix) : T(0);
+                  }
+                }
+              }
+            }
+          });
+        }
+      }
+
+      mbar_wait(bar0 + 8 * (n % NS), (n / NS) & 1);
+
+      if (compute && live) {
+        // register window: planes z-RZ..z+RZ are slots n-2RZ..n
+        T w[2 * RZ + 1][VY + 2 * RY][VX + 2 * RX];
+#pragma unroll
+        for (int dz = 0; dz <= 2 * RZ; ++dz) {
+          const unsigned s = (n - 2 * RZ + dz) % NS;
+          const T *sp = reinterpret_cast<const T *>(smem + s * G::STAGE_BYTES);
+#pragma unroll
+          for (int r = 0; r < VY + 2 * RY; ++r) {
+            const T *row = sp + (ly + r) * G::SXP + HX + lx;  // (ly + r - RY) + RY rows down
+            T ctr[VX];
+            lds_vec<T, VX>(ctr, row);
+#pragma unroll
+            for (int i = 0; i < VX; ++i) w[dz][r][RX + i] = ctr[i];
+#pragma unroll
+            for (int i = 0; i < RX; ++i) {
+              w[dz][r][i] = row[i - RX];
+              w[dz][r][RX + VX + i] = row[VX + i];
+            }
+          }
+        }
+        const bool zin = z >= p.blo[0] && z < p.bhi[0];
+        static_for<VY>([&](auto iyc) {
+          constexpr int IY = decltype(iyc)::value;
+          const int y = gy + IY;
+          if (y < p.whi[1] && y >= p.wlo[1]) {
+            const bool yin = zin && y >= p.blo[1] && y < p.bhi[1];
+            T res[VX];
+            static_for<VX>([&](auto ixc) {
+              constexpr int IX = decltype(ixc)::value;
+              const int x = gx + IX;
+              T v = w[RZ][IY + RY][IX + RX];  // copy-through value: input 0 at this point
+              if (yin && x >= p.blo[2] && x < p.bhi[2]) {
+                WinAcc<F, G, VY, IY, IX> acc{w, pw};
+                v = F::template eval<FMA>(acc, p.c);
+              }
+              res[IX] = v;
+            });
+            T *dst = p.out + (long long)z * p.out_sz + (long long)y * p.out_sy + gx;
+            if (gx >= p.wlo[2] && gx + VX <= p.whi[2]) {
+              stg_vec<T, VX>(dst, res);
+            } else {
+#pragma unroll
+              for (int ix = 0; ix < VX; ++ix)
+                if (gx + ix >= p.wlo[2] && gx + ix < p.whi[2]) dst[ix] = res[ix];
+            }
+          }
+        });
+      }
+
+      if (n >= 2u * RZ) {
+        __syncthreads();  // every thread is done with slot n - 2RZ: its stage may be overwritten
+        if (tid == 0) issue();
+      }
+    }
+  }
+}
+
+}  // namespace neptune

@@ -1,0 +1,829 @@
+// neptune_rt_* — the B200 runtime behind the `neptuneir-to-b200` pipeline (include/neptune_rt.h).
+//
+// Plays the role lib/Runtime/PETSc/NeptunePETScRuntime.cpp plays for `_neptune_rt_runtime_*`
+// in the reference, for the one op this project accelerates: `neptune_ir.apply`, which the
+// reference lowers to malloc + memref.copy + a scalar scf.for nest
+// (lib/Passes/DataflowLowering.cpp:258-448).  Fields live in HBM as identity-layout row-major
+// boxes (NeptuneIRTypeConverter, DataflowLowering.cpp:41-71); a sweep is one launch of a
+// hand-written sm_100a kernel instantiated for the apply's body (kernels/*.cuh).
+// There is no CPU path anywhere in this file: without a CUDA device every entry point fails.
+#include <cuda.h>
+#include <cuda_runtime.h>
+#include <dlfcn.h>
+#include <nccl.h>
+
+#include <algorithm>
+#include <cstdarg>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "frontend/ir.h"
+#include "kernels/registry.h"
+#include "neptune_rt.h"
+
+using neptune::BodyEntry;
+using neptune::BodyInfo;
+using neptune::StencilDesc;
+using neptune::SweepArgs;
+using neptune::Variant;
+
+// ---------------------------------------------------------------------------------------------
+// NCCL is bound at run time: inside a torch process the library torch already loaded is reused
+// (one NCCL per process), elsewhere the system libnccl.so.2 is opened.
+// ---------------------------------------------------------------------------------------------
+namespace {
+struct NcclApi {
+  void *handle = nullptr;
+  ncclResult_t (*GetUniqueId)(ncclUniqueId *) = nullptr;
+  ncclResult_t (*CommInitRank)(ncclComm_t *, int, ncclUniqueId, int) = nullptr;
+  ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
+  ncclResult_t (*Send)(const void *, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
+  ncclResult_t (*Recv)(void *, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
+  ncclResult_t (*GroupStart)() = nullptr;
+  ncclResult_t (*GroupEnd)() = nullptr;
+  const char *(*GetErrorString)(ncclResult_t) = nullptr;
+  bool ok = false;
+};
+
+NcclApi &nccl() {
+  static NcclApi api;
+  static bool tried = false;
+  if (tried) return api;
+  tried = true;
+  const char *names[] = {"libnccl.so.2", "libnccl.so"};
+  for (const char *n : names) {
+    api.handle = dlopen(n, RTLD_NOW | RTLD_NOLOAD | RTLD_GLOBAL);
+    if (api.handle) break;
+  }
+  if (!api.handle) {
+    // a symbol already in the process (torch links its own copy)?
+    if (dlsym(RTLD_DEFAULT, "ncclGetUniqueId")) api.handle = RTLD_DEFAULT;
+  }
+  if (!api.handle)
+    for (const char *n : names) {
+      api.handle = dlopen(n, RTLD_NOW | RTLD_GLOBAL);
+      if (api.handle) break;
+    }
+  if (!api.handle) return api;
+#define NB_SYM(field, sym) api.field = reinterpret_cast<decltype(api.field)>(dlsym(api.handle, sym))
+  NB_SYM(GetUniqueId, "ncclGetUniqueId");
+  NB_SYM(CommInitRank, "ncclCommInitRank");
+  NB_SYM(CommDestroy, "ncclCommDestroy");
+  NB_SYM(Send, "ncclSend");
+  NB_SYM(Recv, "ncclRecv");
+  NB_SYM(GroupStart, "ncclGroupStart");
+  NB_SYM(GroupEnd, "ncclGroupEnd");
+  NB_SYM(GetErrorString, "ncclGetErrorString");
+#undef NB_SYM
+  api.ok = api.GetUniqueId && api.CommInitRank && api.CommDestroy && api.Send && api.Recv && api.GroupStart &&
+           api.GroupEnd && api.GetErrorString;
+  return api;
+}
+
+thread_local std::string g_last_error;
+}  // namespace
+
+// ---------------------------------------------------------------------------------------------
+// handles
+// ---------------------------------------------------------------------------------------------
+struct neptune_rt_ctx {
+  int device = 0;
+  int sm_count = 148;
+  cudaStream_t stream = nullptr;       // sweeps
+  cudaStream_t halo_stream = nullptr;  // halo exchange, high priority
+  cudaEvent_t ev_boundary = nullptr, ev_halo = nullptr;
+  cudaEvent_t ev_t0 = nullptr, ev_t1 = nullptr;
+  int64_t launches = 0;
+  std::string err;
+  ncclComm_t comm = nullptr;
+  int nranks = 1, rank = 0;
+};
+
+struct neptune_rt_field {
+  neptune_rt_ctx *ctx = nullptr;
+  int dtype = NEPTUNE_RT_F64, rank = 1;
+  int64_t lb[3] = {0, 0, 0}, ub[3] = {0, 0, 0};
+  int64_t ext[3] = {1, 1, 1};  // canonical (z, y, x)
+  void *dptr = nullptr;
+  size_t bytes = 0;
+  size_t elsize() const { return dtype == NEPTUNE_RT_F64 ? 8 : 4; }
+  int64_t numel() const { return ext[0] * ext[1] * ext[2]; }
+};
+
+struct TmapEntry {
+  const void *ptr;
+  int64_t nz, ny, nx;
+  int box_x, box_y;
+  CUtensorMap map;
+};
+
+struct neptune_rt_stencil {
+  neptune_rt_ctx *ctx = nullptr;
+  StencilDesc desc;
+  BodyInfo info;
+  const BodyEntry *body = nullptr;
+  bool fma = false;
+  std::string want = "auto";
+  int zchunk = 0;
+  int tblock = 1;
+  const Variant *last = nullptr;
+  std::vector<TmapEntry> tmaps;
+};
+
+namespace {
+
+int set_error(neptune_rt_ctx *ctx, int code, const char *fmt, ...) {
+  char buf[1024];
+  va_list ap;
+  va_start(ap, fmt);
+  std::vsnprintf(buf, sizeof buf, fmt, ap);
+  va_end(ap);
+  g_last_error = buf;
+  if (ctx) ctx->err = buf;
+  return code;
+}
+
+#define RT_CUDA(ctx, call)                                                                                   \
+  do {                                                                                                       \
+    cudaError_t e_ = (call);                                                                                 \
+    if (e_ != cudaSuccess)                                                                                   \
+      return set_error(ctx, NEPTUNE_RT_ECUDA, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, \
+                       __LINE__);                                                                            \
+  } while (0)
+
+#define RT_NCCL(ctx, call)                                                                                     \
+  do {                                                                                                         \
+    ncclResult_t r_ = (call);                                                                                  \
+    if (r_ != ncclSuccess)                                                                                     \
+      return set_error(ctx, NEPTUNE_RT_ENCCL, "%s failed: %s (%s:%d)", #call, nccl().GetErrorString(r_), __FILE__, \
+                       __LINE__);                                                                              \
+  } while (0)
+
+// small device helpers that are not sweeps ----------------------------------------------------
+template <class T> __global__ void fill_kernel(T *p, long long n, T v) {
+  long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  for (; i < n; i += stride) p[i] = v;
+}
+
+// `neptune_ir.store` with bounds: subview x2 + memref.copy (DataflowLowering.cpp:181-218)
+template <class T>
+__global__ void box_copy_kernel(T *dst, const T *src, long long d_sz, long long d_sy, long long s_sz, long long s_sy,
+                                int bz, int by, int bx) {
+  const int x = blockIdx.x * blockDim.x + threadIdx.x;
+  const int y = blockIdx.y * blockDim.y + threadIdx.y;
+  if (x >= bx || y >= by) return;
+  for (int z = blockIdx.z; z < bz; z += gridDim.z)
+    dst[(long long)z * d_sz + (long long)y * d_sy + x] = src[(long long)z * s_sz + (long long)y * s_sy + x];
+}
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
+                                  const cuuint64_t *, const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn encode_tiled() {
+  static EncodeTiledFn fn = nullptr;
+  static bool tried = false;
+  if (!tried) {
+    tried = true;
+    void *p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(p);
+  }
+  return fn;
+}
+
+void canon_box(int rank, const int64_t *lb, const int64_t *ub, int64_t clb[3], int64_t cext[3]) {
+  for (int a = 0; a < 3; ++a) { clb[a] = 0; cext[a] = 1; }
+  for (int d = 0; d < rank; ++d) {
+    clb[3 - rank + d] = lb[d];
+    cext[3 - rank + d] = ub[d] - lb[d];
+  }
+}
+
+}  // namespace
+
+// ---------------------------------------------------------------------------------------------
+// context
+// ---------------------------------------------------------------------------------------------
+extern "C" int neptune_rt_init(int device, neptune_rt_ctx **out) {
+  if (!out) return set_error(nullptr, NEPTUNE_RT_EINVAL, "neptune_rt_init: ctx out-pointer is NULL");
+  *out = nullptr;
+  int ndev = 0;
+  cudaError_t e = cudaGetDeviceCount(&ndev);
+  if (e != cudaSuccess || ndev <= 0)
+    return set_error(nullptr, NEPTUNE_RT_ENODEV,
+                     "neptune_rt_init: no CUDA device (%s); the B200 path has no CPU fallback",
+                     e != cudaSuccess ? cudaGetErrorString(e) : "device count is 0");
+  if (device < 0) {
+    const char *lr = std::getenv("LOCAL_RANK");
+    device = lr ? std::atoi(lr) % ndev : 0;
+  }
+  if (device >= ndev) return set_error(nullptr, NEPTUNE_RT_EINVAL, "neptune_rt_init: device %d of %d", device, ndev);
+  RT_CUDA(nullptr, cudaSetDevice(device));
+  neptune_rt_ctx *c = new neptune_rt_ctx();
+  c->device = device;
+  cudaDeviceProp prop;
+  RT_CUDA(nullptr, cudaGetDeviceProperties(&prop, device));
+  c->sm_count = prop.multiProcessorCount;
+  int lo = 0, hi = 0;
+  cudaDeviceGetStreamPriorityRange(&lo, &hi);
+  RT_CUDA(nullptr, cudaStreamCreateWithPriority(&c->stream, cudaStreamNonBlocking, lo));
+  RT_CUDA(nullptr, cudaStreamCreateWithPriority(&c->halo_stream, cudaStreamNonBlocking, hi));
+  RT_CUDA(nullptr, cudaEventCreateWithFlags(&c->ev_boundary, cudaEventDisableTiming));
+  RT_CUDA(nullptr, cudaEventCreateWithFlags(&c->ev_halo, cudaEventDisableTiming));
+  RT_CUDA(nullptr, cudaEventCreate(&c->ev_t0));
+  RT_CUDA(nullptr, cudaEventCreate(&c->ev_t1));
+  *out = c;
+  return NEPTUNE_RT_OK;
+}
+
+extern "C" int neptune_rt_timer_start(neptune_rt_ctx *c) {
+  if (!c) return set_error(nullptr, NEPTUNE_RT_EINVAL, "timer_start: NULL ctx");
+  RT_CUDA(c, cudaEventRecord(c->ev_t0, c->stream));
+  return NEPTUNE_RT_OK;
+}
+
+extern "C" int neptune_rt_timer_stop(neptune_rt_ctx *c, double *ms) {
+  if (!c || !ms) return set_error(c, NEPTUNE_RT_EINVAL, "timer_stop: NULL argument");
+  RT_CUDA(c, cudaEventRecord(c->ev_t1, c->stream));
+  RT_CUDA(c, cudaEventSynchronize(c->ev_t1));
+  float f = 0;
+  RT_CUDA(c, cudaEventElapsedTime(&f, c->ev_t0, c->ev_t1));
+  *ms = f;
+  return NEPTUNE_RT_OK;
+}
+
+extern "C" int neptune_rt_finalize(neptune_rt_ctx *c) {
+  if (!c) return NEPTUNE_RT_OK;
+  cudaSetDevice(c->device);
+  cudaStreamSynchronize(c->stream);
+  cudaStreamSynchronize(c->halo_stream);
+  if (c->comm && nccl().ok) nccl().CommDestroy(c->comm);
+  cudaEventDestroy(c->ev_boundary);
+  cudaEventDestroy(c->ev_halo);
+  cudaEventDestroy(c->ev_t0);
+  cudaEventDestroy(c->ev_t1);
+  cudaStreamDestroy(c->stream);
+  cudaStreamDestroy(c->halo_stream);
+  delete c;
+  return NEPTUNE_RT_OK;
+}
+
+extern "C" int neptune_rt_sync(neptune_rt_ctx *c) {
+  if (!c) return set_error(nullptr, NEPTUNE_RT_EINVAL, "neptune_rt_sync: NULL ctx");
+  RT_CUDA(c, cudaStreamSynchronize(c->halo_stream));
+  RT_CUDA(c, cudaStreamSynchronize(c->stream));
+  return NEPTUNE_RT_OK;
+}
+
+extern "C" const char *neptune_rt_last_error(neptune_rt_ctx *c) { return c ? c->err.c_str() : g_last_error.c_str(); }
+extern "C" int64_t neptune_rt_launch_count(neptune_rt_ctx *c) { return c ? c->launches : 0; }
+extern "C" void *neptune_rt_stream(neptune_rt_ctx *c) { return c ? (void *)c->stream : nullptr; }
+
+// ---------------------------------------------------------------------------------------------
+// fields
+// ---------------------------------------------------------------------------------------------
+extern "C" int neptune_rt_field_alloc(neptune_rt_ctx *c, int dtype, int rank, const int64_t *lb, const int64_t *ub,
+                                      neptune_rt_field **out) {
+  if (!c || !out || !lb || !ub) return set_error(c, NEPTUNE_RT_EINVAL, "neptune_rt_field_alloc: NULL argument");
+  *out = nullptr;
+  if (rank < 1 || rank > NEPTUNE_RT_MAX_RANK) return set_error(c, NEPTUNE_RT_EINVAL, "field rank %d (1..3)", rank);
+  if (dtype != NEPTUNE_RT_F32 && dtype != NEPTUNE_RT_F64) return set_error(c, NEPTUNE_RT_EINVAL, "field dtype %d", dtype);
+  neptune_rt_field *f = new neptune_rt_field();
+  f->ctx = c; f->dtype = dtype; f->rank = rank;
+  for (int d = 0; d < rank; ++d) {
+    if (ub[d] < lb[d]) { delete f; return set_error(c, NEPTUNE_RT_EINVAL, "field bounds inverted in dim %d", d); }
+    if (ub[d] - lb[d] > 0x7fffffffLL) { delete f; return set_error(c, NEPTUNE_RT_EINVAL, "field extent too large in dim %d", d); }
+    f->lb[d] = lb[d]; f->ub[d] = ub[d];
+  }
+  int64_t clb[3];
+  canon_box(rank, lb, ub, clb, f->ext);
+  f->bytes = (size_t)f->numel() * f->elsize();
+  cudaSetDevice(c->device);
+  cudaError_t e = cudaMalloc(&f->dptr, std::max<size_t>(f->bytes, 16) + 256);  // slack keeps vector tails in-bounds
+  if (e != cudaSuccess) {
+    delete f;
+    return set_error(c, e == cudaErrorMemoryAllocation ? NEPTUNE_RT_ENOMEM : NEPTUNE_RT_ECUDA,
+                     "cudaMalloc of a %zu-byte field failed: %s", (size_t)0 + f->bytes, cudaGetErrorString(e));
+  }
+  *out = f;
+  return NEPTUNE_RT_OK;
+}
+
+extern "C" int neptune_rt_field_free(neptune_rt_field *f) {
+  if (!f) return NEPTUNE_RT_OK;
+  cudaSetDevice(f->ctx->device);
+  cudaStreamSynchronize(f->ctx->stream);
+  cudaFree(f->dptr);
+  delete f;
+  return NEPTUNE_RT_OK;
+}
+
+static int plane_range(neptune_rt_field *f, int64_t p0, int64_t p1, size_t *off, size_t *len) {
+  const int cd0 = 3 - f->rank;
+  const int64_t n0 = f->ext[cd0];
+  if (p0 < 0 || p1 > n0 || p0 > p1) return set_error(f->ctx, NEPTUNE_RT_EINVAL, "plane range [%lld, %lld) of %lld", (long long)p0, (long long)p1, (long long)n0);
+  const size_t plane = n0 ? f->bytes / (size_t)n0 : 0;
+  *off = (size_t)p0 * plane;
+  *len = (size_t)(p1 - p0) * plane;
+  return NEPTUNE_RT_OK;
+}
+
+extern "C" int neptune_rt_field_upload_planes(neptune_rt_field *f, const void *host, int64_t p0, int64_t p1) {
+  if (!f || !host) return set_error(f ? f->ctx : nullptr, NEPTUNE_RT_EINVAL, "field_upload: NULL argument");
+  size_t off, len;
+  if (int rc = plane_range(f, p0, p1, &off, &len)) return rc;
+  if (!len) return NEPTUNE_RT_OK;
+  RT_CUDA(f->ctx, cudaMemcpyAsync((char *)f->dptr + off, (const char *)host + off, len, cudaMemcpyHostToDevice, f->ctx->stream));
+  return NEPTUNE_RT_OK;
+}
+extern "C" int neptune_rt_field_download_planes(neptune_rt_field *f, void *host, int64_t p0, int64_t p1) {
+  if (!f || !host) return set_error(f ? f->ctx : nullptr, NEPTUNE_RT_EINVAL, "field_download: NULL argument");
+  size_t off, len;
+  if (int rc = plane_range(f, p0, p1, &off, &len)) return rc;
+  if (!len) return NEPTUNE_RT_OK;
+  RT_CUDA(f->ctx, cudaMemcpyAsync((char *)host + off, (const char *)f->dptr + off, len, cudaMemcpyDeviceToHost, f->ctx->stream));
+  return NEPTUNE_RT_OK;
+}
+extern "C" int neptune_rt_field_upload(neptune_rt_field *f, const void *host) {
+  if (!f) return set_error(nullptr, NEPTUNE_RT_EINVAL, "field_upload: NULL field");
+  return neptune_rt_field_upload_planes(f, host, 0, f->ext[3 - f->rank]);
+}
+extern "C" int neptune_rt_field_download(neptune_rt_field *f, void *host) {
+  if (!f) return set_error(nullptr, NEPTUNE_RT_EINVAL, "field_download: NULL field");
+  return neptune_rt_field_download_planes(f, host, 0, f->ext[3 - f->rank]);
+}
+
+extern "C" int neptune_rt_field_fill(neptune_rt_field *f, double value) {
+  if (!f) return set_error(nullptr, NEPTUNE_RT_EINVAL, "field_fill: NULL field");
+  const long long n = f->numel();
+  if (!n) return NEPTUNE_RT_OK;
+  const int grid = (int)std::min<long long>((n + 255) / 256, (long long)f->ctx->sm_count * 8);
+  if (f->dtype == NEPTUNE_RT_F64) fill_kernel<double><<<grid, 256, 0, f->ctx->stream>>>((double *)f->dptr, n, value);
+  else fill_kernel<float><<<grid, 256, 0, f->ctx->stream>>>((float *)f->dptr, n, (float)value);
+  RT_CUDA(f->ctx, cudaGetLastError());
+  f->ctx->launches++;
+  return NEPTUNE_RT_OK;
+}
+
+extern "C" void *neptune_rt_field_device_ptr(neptune_rt_field *f) { return f ? f->dptr : nullptr; }
+extern "C" int64_t neptune_rt_field_bytes(neptune_rt_field *f) { return f ? (int64_t)f->bytes : 0; }
+
+extern "C" int neptune_rt_field_store(neptune_rt_field *dst, neptune_rt_field *src, const int64_t *lb, const int64_t *ub) {
+  if (!dst || !src) return set_error(nullptr, NEPTUNE_RT_EINVAL, "field_store: NULL field");
+  neptune_rt_ctx *c = dst->ctx;
+  if (dst->rank != src->rank || dst->dtype != src->dtype) return set_error(c, NEPTUNE_RT_EINVAL, "field_store: rank/dtype mismatch");
+  if (!lb || !ub) {
+    // whole memref.copy (DataflowLowering.cpp:176-179): shapes must agree
+    for (int a = 0; a < 3; ++a)
+      if (dst->ext[a] != src->ext[a]) return set_error(c, NEPTUNE_RT_EINVAL, "field_store: extents differ");
+    if (dst->dptr != src->dptr && dst->bytes)
+      RT_CUDA(c, cudaMemcpyAsync(dst->dptr, src->dptr, dst->bytes, cudaMemcpyDeviceToDevice, c->stream));
+    return NEPTUNE_RT_OK;
+  }
+  int64_t blb[3], bext[3];
+  canon_box(dst->rank, lb, ub, blb, bext);
+  int64_t slb[3], dlb[3], tmp[3];
+  canon_box(src->rank, src->lb, src->ub, slb, tmp);
+  canon_box(dst->rank, dst->lb, dst->ub, dlb, tmp);
+  for (int a = 0; a < 3; ++a) {
+    if (bext[a] <= 0) return NEPTUNE_RT_OK;
+    if (blb[a] < slb[a] || blb[a] + bext[a] > slb[a] + src->ext[a] || blb[a] < dlb[a] || blb[a] + bext[a] > dlb[a] + dst->ext[a])
+      return set_error(c, NEPTUNE_RT_EINVAL, "field_store: bounds leave the source or destination box");
+  }
+  const long long s_sy = src->ext[2], s_sz = src->ext[1] * src->ext[2], d_sy = dst->ext[2], d_sz = dst->ext[1] * dst->ext[2];
+  const long long soff = (blb[0] - slb[0]) * s_sz + (blb[1] - slb[1]) * s_sy + (blb[2] - slb[2]);
+  const long long doff = (blb[0] - dlb[0]) * d_sz + (blb[1] - dlb[1]) * d_sy + (blb[2] - dlb[2]);
+  dim3 block(128, 2, 1);
+  dim3 grid((unsigned)((bext[2] + 127) / 128), (unsigned)((bext[1] + 1) / 2), (unsigned)std::min<int64_t>(bext[0], 1024));
+  if (grid.y > 65535u) return set_error(c, NEPTUNE_RT_EINVAL, "field_store: box too tall");
+  if (dst->dtype == NEPTUNE_RT_F64)
+    box_copy_kernel<double><<<grid, block, 0, c->stream>>>((double *)dst->dptr + doff, (const double *)src->dptr + soff, d_sz, d_sy, s_sz, s_sy, (int)bext[0], (int)bext[1], (int)bext[2]);
+  else
+    box_copy_kernel<float><<<grid, block, 0, c->stream>>>((float *)dst->dptr + doff, (const float *)src->dptr + soff, d_sz, d_sy, s_sz, s_sy, (int)bext[0], (int)bext[1], (int)bext[2]);
+  RT_CUDA(c, cudaGetLastError());
+  c->launches++;
+  return NEPTUNE_RT_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// stencils
+// ---------------------------------------------------------------------------------------------
+extern "C" uint64_t neptune_rt_body_key(const neptune_rt_stencil_desc *d) { return d ? neptune::body_key(*d) : 0; }
+extern "C" int neptune_rt_body_compiled(uint64_t key) { return neptune::find_body(key) ? 1 : 0; }
+
+extern "C" int neptune_rt_stencil_create(neptune_rt_ctx *c, const neptune_rt_stencil_desc *d, neptune_rt_stencil **out) {
+  if (!c || !d || !out) return set_error(c, NEPTUNE_RT_EINVAL, "neptune_rt_stencil_create: NULL argument");
+  *out = nullptr;
+  try {
+    neptune::validate_desc(*d);
+  } catch (const neptune::Diagnostic &e) {
+    return set_error(c, e.unsupported ? NEPTUNE_RT_EUNSUPPORTED : NEPTUNE_RT_EINVAL, "%s", e.what());
+  }
+  const uint64_t key = neptune::body_key(*d);
+  const BodyEntry *be = neptune::find_body(key);
+  if (!be)
+    return set_error(c, NEPTUNE_RT_EUNSUPPORTED,
+                     "apply body with structure key 0x%016llx is not in the compiled sm_100a kernel catalogue "
+                     "(%zu bodies); add its .mlir to the catalogue and rebuild — there is no CPU fallback",
+                     (unsigned long long)key, neptune::all_bodies().size());
+  neptune_rt_stencil *s = new neptune_rt_stencil();
+  s->ctx = c;
+  s->desc = StencilDesc::from_c(*d);
+  s->info = neptune::analyze_body(s->desc.c);
+  s->body = be;
+  s->fma = (d->flags & NEPTUNE_RT_FLAG_FMA) != 0;
+  *out = s;
+  return NEPTUNE_RT_OK;
+}
+
+extern "C" int neptune_rt_stencil_destroy(neptune_rt_stencil *s) {
+  delete s;
+  return NEPTUNE_RT_OK;
+}
+
+extern "C" int neptune_rt_stencil_set(neptune_rt_stencil *s, const char *key, const char *value) {
+  if (!s || !key || !value) return set_error(s ? s->ctx : nullptr, NEPTUNE_RT_EINVAL, "stencil_set: NULL argument");
+  const std::string k = key, v = value;
+  if (k == "variant") {
+    if (v != "auto") {
+      bool found = false;
+      for (auto &var : s->body->variants) found |= var.name == v;
+      if (!found) return set_error(s->ctx, NEPTUNE_RT_EINVAL, "stencil_set: this body has no kernel variant '%s'", value);
+    }
+    s->want = v;
+    return NEPTUNE_RT_OK;
+  }
+  if (k == "zchunk") { s->zchunk = std::max(0, std::atoi(value)); return NEPTUNE_RT_OK; }
+  if (k == "tblock") {
+    const int t = std::atoi(value);
+    if (t < 1 || t > 8) return set_error(s->ctx, NEPTUNE_RT_EINVAL, "stencil_set: tblock must be 1..8");
+    s->tblock = t;
+    return NEPTUNE_RT_OK;
+  }
+  if (k == "fma") { s->fma = v == "1" || v == "true"; return NEPTUNE_RT_OK; }
+  return set_error(s->ctx, NEPTUNE_RT_EINVAL, "stencil_set: unknown key '%s'", key);
+}
+
+extern "C" int neptune_rt_stencil_variant_count(neptune_rt_stencil *s) {
+  if (!s) return 0;
+  int n = 0;
+  for (auto &v : s->body->variants) n += v.fma == false;
+  return n;
+}
+extern "C" const char *neptune_rt_stencil_variant_name(neptune_rt_stencil *s, int index) {
+  if (!s) return nullptr;
+  int n = 0;
+  for (auto &v : s->body->variants)
+    if (!v.fma && n++ == index) return v.name.c_str();
+  return nullptr;
+}
+
+extern "C" const char *neptune_rt_stencil_variant(neptune_rt_stencil *s) {
+  return (s && s->last) ? s->last->name.c_str() : "";
+}
+
+namespace {
+
+int get_tmap(neptune_rt_stencil *s, const void *ptr, const int64_t ext[3], int box_x, int box_y, const CUtensorMap **out) {
+  for (auto &e : s->tmaps)
+    if (e.ptr == ptr && e.nz == ext[0] && e.ny == ext[1] && e.nx == ext[2] && e.box_x == box_x && e.box_y == box_y) {
+      *out = &e.map;
+      return NEPTUNE_RT_OK;
+    }
+  EncodeTiledFn enc = encode_tiled();
+  if (!enc) return set_error(s->ctx, NEPTUNE_RT_ECUDA, "cuTensorMapEncodeTiled is not available from this driver");
+  const size_t S = s->desc.c.dtype == NEPTUNE_RT_F64 ? 8 : 4;
+  TmapEntry e;
+  e.ptr = ptr; e.nz = ext[0]; e.ny = ext[1]; e.nx = ext[2]; e.box_x = box_x; e.box_y = box_y;
+  cuuint64_t dims[3] = {(cuuint64_t)ext[2], (cuuint64_t)ext[1], (cuuint64_t)ext[0]};
+  cuuint64_t strides[2] = {(cuuint64_t)ext[2] * S, (cuuint64_t)ext[2] * (cuuint64_t)ext[1] * S};
+  cuuint32_t box[3] = {(cuuint32_t)box_x, (cuuint32_t)box_y, 1};
+  cuuint32_t estr[3] = {1, 1, 1};
+  CUresult r = enc(&e.map, S == 8 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT64 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3,
+                   const_cast<void *>(ptr), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                   CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return set_error(s->ctx, NEPTUNE_RT_ECUDA, "cuTensorMapEncodeTiled failed with CUresult %d", (int)r);
+  if (s->tmaps.size() >= 64) s->tmaps.erase(s->tmaps.begin());
+  s->tmaps.push_back(e);
+  *out = &s->tmaps.back().map;
+  return NEPTUNE_RT_OK;
+}
+
+// Can the TMA-staged kernel take this launch?  It assumes every input shares the result's box
+// (so that one set of coordinates addresses all of them) and 16-byte aligned rows.
+bool tma_eligible(const neptune_rt_stencil *s, int n_in, neptune_rt_field *const *in, const neptune_rt_field *out) {
+  const size_t S = out->elsize();
+  const int VX = (int)(16 / S);
+  if (out->ext[2] % VX) return false;
+  if ((uintptr_t)out->dptr % 16) return false;
+  for (int k = 0; k < n_in; ++k) {
+    for (int a = 0; a < 3; ++a)
+      if (in[k]->ext[a] != out->ext[a]) return false;
+    for (int d = 0; d < out->rank; ++d)
+      if (in[k]->lb[d] != out->lb[d]) return false;
+    if ((uintptr_t)in[k]->dptr % 16) return false;
+  }
+  (void)s;
+  return true;
+}
+
+int do_apply(neptune_rt_stencil *s, int n_in, neptune_rt_field *const *in, neptune_rt_field *out, int64_t p0, int64_t p1,
+             cudaStream_t stream) {
+  neptune_rt_ctx *c = s->ctx;
+  const neptune_rt_stencil_desc &d = s->desc.c;
+  if (n_in != d.n_inputs) return set_error(c, NEPTUNE_RT_EINVAL, "neptune_rt_apply: %d inputs given, the apply has %d", n_in, d.n_inputs);
+  if (!in || !out) return set_error(c, NEPTUNE_RT_EINVAL, "neptune_rt_apply: NULL field");
+  if (out->rank != d.rank || out->dtype != d.dtype) return set_error(c, NEPTUNE_RT_EINVAL, "neptune_rt_apply: result field rank/dtype differ from the apply");
+  for (int a = 0; a < d.rank; ++a)
+    if (out->lb[a] != d.out_lb[a] || out->ub[a] != d.out_ub[a])
+      return set_error(c, NEPTUNE_RT_EINVAL, "neptune_rt_apply: result field bounds differ from the apply's result type");
+  SweepArgs a;
+  for (int k = 0; k < n_in; ++k) {
+    neptune_rt_field *f = in[k];
+    if (!f) return set_error(c, NEPTUNE_RT_EINVAL, "neptune_rt_apply: input %d is NULL", k);
+    if (f->rank != d.rank || f->dtype != d.dtype) return set_error(c, NEPTUNE_RT_EINVAL, "neptune_rt_apply: input %d rank/dtype differ from the apply", k);
+    for (int x = 0; x < d.rank; ++x)
+      if (f->lb[x] != d.in_lb[(size_t)k * d.rank + x] || f->ub[x] != d.in_ub[(size_t)k * d.rank + x])
+        return set_error(c, NEPTUNE_RT_EINVAL, "neptune_rt_apply: input %d bounds differ from the apply's operand type", k);
+    if (f->dptr == out->dptr)
+      return set_error(c, NEPTUNE_RT_EINVAL, "neptune_rt_apply: the result aliases input %d (the reference allocates a fresh result, DataflowLowering.cpp:273-281)", k);
+  }
+  const int cd0 = 3 - d.rank;
+  if (p0 < 0 || p1 > out->ext[cd0] || p0 > p1) return set_error(c, NEPTUNE_RT_EINVAL, "neptune_rt_apply_planes: plane range [%lld, %lld)", (long long)p0, (long long)p1);
+  if (p0 == p1 || out->numel() == 0) return NEPTUNE_RT_OK;
+
+  const size_t S = out->elsize();
+  a.out = out->dptr;
+  a.out_sy = out->ext[2];
+  a.out_sz = out->ext[1] * out->ext[2];
+  a.nz = (int)out->ext[0]; a.ny = (int)out->ext[1]; a.nx = (int)out->ext[2];
+  int64_t olb[3], tmp[3];
+  canon_box(d.rank, d.out_lb, d.out_ub, olb, tmp);
+  for (int k = 0; k < n_in; ++k) {
+    int64_t ilb[3], iext[3];
+    canon_box(d.rank, in[k]->lb, in[k]->ub, ilb, iext);
+    a.in_sy[k] = iext[2];
+    a.in_sz[k] = iext[1] * iext[2];
+    // tap address = base + ((p + off) - in_lb) with p = q + out_lb   (DataflowLowering.cpp:381-411)
+    const long long shift = (olb[0] - ilb[0]) * a.in_sz[k] + (olb[1] - ilb[1]) * a.in_sy[k] + (olb[2] - ilb[2]);
+    a.in[k] = (const char *)in[k]->dptr + shift * (long long)S;
+  }
+  a.copy_src = in[0]->dptr;
+  int64_t blb[3], bext[3];
+  canon_box(d.rank, d.lb, d.ub, blb, bext);
+  bool empty = false;
+  for (int x = 0; x < d.rank; ++x) empty |= d.ub[x] <= d.lb[x];
+  for (int x = 0; x < 3; ++x) {
+    a.blo[x] = empty ? 0 : (int)(blb[x] - olb[x]);
+    a.bhi[x] = empty ? 0 : (int)(blb[x] - olb[x] + bext[x]);
+    a.wlo[x] = 0;
+    a.whi[x] = (int)out->ext[x];
+  }
+  a.wlo[cd0] = (int)p0;
+  a.whi[cd0] = (int)p1;
+  for (int i = 0; i < s->info.n_consts; ++i) a.consts[i] = s->info.consts[i];
+  a.zchunk = s->zchunk;
+  a.sm_count = c->sm_count;
+  a.stream = stream;
+
+  // pick the kernel variant
+  const Variant *pick = nullptr;
+  const bool tma_ok = tma_eligible(s, n_in, in, out) && encode_tiled() != nullptr;
+  if (s->want == "auto") {
+    if (tma_ok)
+      for (auto &v : s->body->variants)
+        if (v.kind == neptune::VARIANT_TMA && v.fma == s->fma) { pick = &v; break; }
+    if (!pick)
+      for (auto &v : s->body->variants)
+        if (v.kind == neptune::VARIANT_DIRECT && v.fma == s->fma) { pick = &v; break; }
+  } else {
+    for (auto &v : s->body->variants)
+      if (v.name == s->want && v.fma == s->fma) { pick = &v; break; }
+    if (!pick)
+      for (auto &v : s->body->variants)
+        if (v.name == s->want) { pick = &v; break; }
+    if (pick && pick->kind == neptune::VARIANT_TMA && !tma_ok)
+      return set_error(c, NEPTUNE_RT_EINVAL, "kernel variant '%s' needs inputs that share the result's box and 16-byte aligned rows", pick->name.c_str());
+  }
+  if (!pick) return set_error(c, NEPTUNE_RT_EUNSUPPORTED, "no kernel variant '%s' for this body", s->want.c_str());
+  if (pick->kind == neptune::VARIANT_TMA) {
+    const CUtensorMap *tm = nullptr;
+    if (int rc = get_tmap(s, in[s->body->staged]->dptr, in[s->body->staged]->ext, pick->box_x, pick->box_y, &tm)) return rc;
+    a.tmap = tm;
+  }
+  cudaSetDevice(c->device);
+  const int e = pick->launch(a);
+  if (e != 0) return set_error(c, NEPTUNE_RT_ECUDA, "launch of sweep kernel '%s' failed: %s", pick->name.c_str(), cudaGetErrorString((cudaError_t)e));
+  s->last = pick;
+  c->launches++;
+  return NEPTUNE_RT_OK;
+}
+
+}  // namespace
+
+extern "C" int neptune_rt_apply(neptune_rt_stencil *s, int n_in, neptune_rt_field *const *in, neptune_rt_field *out) {
+  if (!s || !out) return set_error(s ? s->ctx : nullptr, NEPTUNE_RT_EINVAL, "neptune_rt_apply: NULL argument");
+  return do_apply(s, n_in, in, out, 0, out->ext[3 - out->rank], s->ctx->stream);
+}
+
+extern "C" int neptune_rt_apply_planes(neptune_rt_stencil *s, int n_in, neptune_rt_field *const *in, neptune_rt_field *out,
+                                       int64_t p0, int64_t p1, void *stream) {
+  if (!s || !out) return set_error(s ? s->ctx : nullptr, NEPTUNE_RT_EINVAL, "neptune_rt_apply_planes: NULL argument");
+  return do_apply(s, n_in, in, out, p0, p1, stream ? (cudaStream_t)stream : s->ctx->stream);
+}
+
+// ---------------------------------------------------------------------------------------------
+// slab decomposition + halos
+// ---------------------------------------------------------------------------------------------
+extern "C" int neptune_rt_slab_partition(int64_t n0, int nranks, int rank, int64_t *begin, int64_t *end) {
+  if (nranks < 1 || rank < 0 || rank >= nranks || n0 < 0 || !begin || !end)
+    return set_error(nullptr, NEPTUNE_RT_EINVAL, "slab_partition: bad arguments");
+  const int64_t base = n0 / nranks, rem = n0 % nranks;
+  *begin = rank * base + std::min<int64_t>(rank, rem);
+  *end = *begin + base + (rank < rem ? 1 : 0);
+  return NEPTUNE_RT_OK;
+}
+
+extern "C" int neptune_rt_slab_localize(const neptune_rt_stencil_desc *g, int nranks, int rank, int64_t halo,
+                                        neptune_rt_stencil_desc *l, int64_t *lin_lb, int64_t *lin_ub) {
+  if (!g || !l || !lin_lb || !lin_ub || halo < 0) return set_error(nullptr, NEPTUNE_RT_EINVAL, "slab_localize: bad arguments");
+  try {
+    neptune::validate_desc(*g);
+  } catch (const neptune::Diagnostic &e) {
+    return set_error(nullptr, e.unsupported ? NEPTUNE_RT_EUNSUPPORTED : NEPTUNE_RT_EINVAL, "%s", e.what());
+  }
+  int64_t b, e;
+  if (int rc = neptune_rt_slab_partition(g->out_ub[0] - g->out_lb[0], nranks, rank, &b, &e)) return rc;
+  const int64_t own_lo = g->out_lb[0] + b, own_hi = g->out_lb[0] + e;
+  // every tap must stay inside own +- halo
+  for (int i = 0; i < g->n_ops; ++i)
+    if (g->ops[i].opcode == NEPTUNE_RT_OP_ACCESS && std::llabs(g->ops[i].offset[0]) > halo)
+      return set_error(nullptr, NEPTUNE_RT_EINVAL, "slab_localize: halo %lld is narrower than the dim-0 stencil radius", (long long)halo);
+  for (int k = 0; k < g->n_inputs; ++k)
+    if (g->in_lb[(size_t)k * g->rank] != g->out_lb[0] || g->in_ub[(size_t)k * g->rank] != g->out_ub[0])
+      return set_error(nullptr, NEPTUNE_RT_EUNSUPPORTED, "slab_localize: inputs must share the result's dim-0 bounds");
+  *l = *g;
+  std::memcpy(lin_lb, g->in_lb, sizeof(int64_t) * (size_t)g->n_inputs * g->rank);
+  std::memcpy(lin_ub, g->in_ub, sizeof(int64_t) * (size_t)g->n_inputs * g->rank);
+  const int64_t lo = std::max(g->out_lb[0], own_lo - halo), hi = std::min(g->out_ub[0], own_hi + halo);
+  l->out_lb[0] = lo; l->out_ub[0] = hi;
+  for (int k = 0; k < g->n_inputs; ++k) { lin_lb[(size_t)k * g->rank] = lo; lin_ub[(size_t)k * g->rank] = hi; }
+  l->in_lb = lin_lb; l->in_ub = lin_ub;
+  l->lb[0] = std::max(g->lb[0], own_lo);
+  l->ub[0] = std::max(l->lb[0], std::min(g->ub[0], own_hi));
+  return NEPTUNE_RT_OK;
+}
+
+extern "C" int neptune_rt_comm_unique_id(void *id128) {
+  if (!id128) return set_error(nullptr, NEPTUNE_RT_EINVAL, "comm_unique_id: NULL");
+  if (!nccl().ok) return set_error(nullptr, NEPTUNE_RT_ENCCL, "NCCL (libnccl.so.2) could not be loaded");
+  static_assert(sizeof(ncclUniqueId) == 128, "ncclUniqueId is 128 bytes");
+  ncclUniqueId id;
+  RT_NCCL(nullptr, nccl().GetUniqueId(&id));
+  std::memcpy(id128, &id, 128);
+  return NEPTUNE_RT_OK;
+}
+
+extern "C" int neptune_rt_comm_init(neptune_rt_ctx *c, const void *id128, int nranks, int rank) {
+  if (!c || !id128 || nranks < 1 || rank < 0 || rank >= nranks) return set_error(c, NEPTUNE_RT_EINVAL, "comm_init: bad arguments");
+  if (!nccl().ok) return set_error(c, NEPTUNE_RT_ENCCL, "NCCL (libnccl.so.2) could not be loaded");
+  ncclUniqueId id;
+  std::memcpy(&id, id128, 128);
+  cudaSetDevice(c->device);
+  RT_NCCL(c, nccl().CommInitRank(&c->comm, nranks, id, rank));
+  c->nranks = nranks;
+  c->rank = rank;
+  return NEPTUNE_RT_OK;
+}
+
+extern "C" int neptune_rt_halo_exchange(neptune_rt_ctx *c, neptune_rt_field *f, int64_t own_begin, int64_t own_end,
+                                        int64_t width, void *stream_) {
+  if (!c || !f) return set_error(c, NEPTUNE_RT_EINVAL, "halo_exchange: NULL argument");
+  if (c->nranks == 1 || width == 0) return NEPTUNE_RT_OK;
+  if (!c->comm) return set_error(c, NEPTUNE_RT_ENCCL, "halo_exchange: no communicator (neptune_rt_comm_init)");
+  cudaStream_t st = stream_ ? (cudaStream_t)stream_ : c->halo_stream;
+  const int cd0 = 3 - f->rank;
+  const int64_t n0 = f->ext[cd0];
+  const size_t plane = n0 ? f->bytes / (size_t)n0 : 0;
+  const bool up = c->rank > 0, down = c->rank + 1 < c->nranks;
+  if (own_end - own_begin < width) return set_error(c, NEPTUNE_RT_EINVAL, "halo_exchange: slab thinner than the halo");
+  if ((up && own_begin < width) || (down && own_end + width > n0))
+    return set_error(c, NEPTUNE_RT_EINVAL, "halo_exchange: field has no room for %lld ghost planes", (long long)width);
+  char *base = (char *)f->dptr;
+  const size_t n = plane * (size_t)width;
+  RT_NCCL(c, nccl().GroupStart());
+  if (up) {
+    RT_NCCL(c, nccl().Send(base + (size_t)own_begin * plane, n, ncclChar, c->rank - 1, c->comm, st));
+    RT_NCCL(c, nccl().Recv(base + (size_t)(own_begin - width) * plane, n, ncclChar, c->rank - 1, c->comm, st));
+  }
+  if (down) {
+    RT_NCCL(c, nccl().Send(base + (size_t)(own_end - width) * plane, n, ncclChar, c->rank + 1, c->comm, st));
+    RT_NCCL(c, nccl().Recv(base + (size_t)own_end * plane, n, ncclChar, c->rank + 1, c->comm, st));
+  }
+  RT_NCCL(c, nccl().GroupEnd());
+  return NEPTUNE_RT_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// time loop
+// ---------------------------------------------------------------------------------------------
+extern "C" int neptune_rt_run_steps(neptune_rt_stencil *s, neptune_rt_field *fa, neptune_rt_field *fb, int n_extra,
+                                    neptune_rt_field *const *extra, int64_t nsteps, neptune_rt_field **result) {
+  if (!s || !fa || !fb) return set_error(s ? s->ctx : nullptr, NEPTUNE_RT_EINVAL, "run_steps: NULL argument");
+  neptune_rt_ctx *c = s->ctx;
+  const neptune_rt_stencil_desc &d = s->desc.c;
+  if (n_extra != d.n_inputs - 1) return set_error(c, NEPTUNE_RT_EINVAL, "run_steps: %d extra inputs given, the apply has %d", n_extra, d.n_inputs - 1);
+  neptune_rt_field *ins[NEPTUNE_RT_MAX_INPUTS];
+  for (int k = 0; k < n_extra; ++k) ins[k + 1] = extra[k];
+  neptune_rt_field *cur = fa, *nxt = fb;
+  const int cd0 = 3 - d.rank;
+  const int64_t n0 = fa->ext[cd0];
+
+  if (c->nranks == 1 || !c->comm) {
+    for (int64_t t = 0; t < nsteps; ++t) {
+      ins[0] = cur;
+      if (int rc = do_apply(s, d.n_inputs, ins, nxt, 0, n0, c->stream)) return rc;
+      std::swap(cur, nxt);
+    }
+    if (result) *result = cur;
+    return NEPTUNE_RT_OK;
+  }
+
+  // slab mode: the local box is [own - halo, own + halo) clipped to the global box, as built by
+  // neptune_rt_slab_localize; ghost planes exist on the sides that have a neighbour
+  int64_t halo = 0;
+  for (int i = 0; i < d.n_ops; ++i)
+    if (d.ops[i].opcode == NEPTUNE_RT_OP_ACCESS) halo = std::max<int64_t>(halo, std::llabs(d.ops[i].offset[0]));
+  const bool up = c->rank > 0, down = c->rank + 1 < c->nranks;
+  const int64_t own_b = up ? halo : 0, own_e = n0 - (down ? halo : 0);
+  if (own_e - own_b < 2 * halo) return set_error(c, NEPTUNE_RT_EINVAL, "run_steps: slab of %lld planes is thinner than two halos", (long long)(own_e - own_b));
+  // ghosts of the first input state
+  RT_CUDA(c, cudaEventRecord(c->ev_boundary, c->stream));
+  RT_CUDA(c, cudaStreamWaitEvent(c->halo_stream, c->ev_boundary, 0));
+  if (int rc = neptune_rt_halo_exchange(c, cur, own_b, own_e, halo, c->halo_stream)) return rc;
+  RT_CUDA(c, cudaEventRecord(c->ev_halo, c->halo_stream));
+  RT_CUDA(c, cudaStreamWaitEvent(c->stream, c->ev_halo, 0));
+  for (int64_t t = 0; t < nsteps; ++t) {
+    ins[0] = cur;
+    // 1. boundary planes of the owned slab, so their exchange can start early
+    if (halo > 0) {
+      if (up) if (int rc = do_apply(s, d.n_inputs, ins, nxt, own_b, own_b + halo, c->stream)) return rc;
+      if (down) if (int rc = do_apply(s, d.n_inputs, ins, nxt, own_e - halo, own_e, c->stream)) return rc;
+    }
+    RT_CUDA(c, cudaEventRecord(c->ev_boundary, c->stream));
+    RT_CUDA(c, cudaStreamWaitEvent(c->halo_stream, c->ev_boundary, 0));
+    // 2. halo exchange of the new state on the high-priority stream, concurrent with 3.
+    if (int rc = neptune_rt_halo_exchange(c, nxt, own_b, own_e, halo, c->halo_stream)) return rc;
+    RT_CUDA(c, cudaEventRecord(c->ev_halo, c->halo_stream));
+    // 3. interior
+    if (int rc = do_apply(s, d.n_inputs, ins, nxt, own_b + (up ? halo : 0), own_e - (down ? halo : 0), c->stream)) return rc;
+    // 4. join
+    RT_CUDA(c, cudaStreamWaitEvent(c->stream, c->ev_halo, 0));
+    std::swap(cur, nxt);
+  }
+  if (result) *result = cur;
+  return NEPTUNE_RT_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// memref-level entry point for MLIR-generated code
+// ---------------------------------------------------------------------------------------------
+static neptune_rt_ctx *default_ctx() {
+  static neptune_rt_ctx *ctx = nullptr;
+  if (!ctx && neptune_rt_init(-1, &ctx) != NEPTUNE_RT_OK) {
+    std::fprintf(stderr, "[NeptuneRT-B200] %s\n", neptune_rt_last_error(nullptr));
+    std::abort();
+  }
+  return ctx;
+}
+
+extern "C" void neptune_rt_apply_memref(const neptune_rt_stencil_desc *d, int n_in, const void *const *in_host, void *out_host) {
+  neptune_rt_ctx *c = default_ctx();
+  auto die = [&](const char *what) {
+    std::fprintf(stderr, "[NeptuneRT-B200] %s: %s\n", what, neptune_rt_last_error(c));
+    std::abort();  // generated code does not check statuses (NeptunePETScRuntime.cpp:15-30)
+  };
+  if (!d || !in_host || !out_host || n_in != d->n_inputs) { set_error(c, NEPTUNE_RT_EINVAL, "bad arguments"); die("neptune_rt_apply_memref"); }
+  neptune_rt_stencil *s = nullptr;
+  if (neptune_rt_stencil_create(c, d, &s)) die("neptune_rt_stencil_create");
+  std::vector<neptune_rt_field *> ins(n_in, nullptr);
+  for (int k = 0; k < n_in; ++k) {
+    if (neptune_rt_field_alloc(c, d->dtype, d->rank, d->in_lb + (size_t)k * d->rank, d->in_ub + (size_t)k * d->rank, &ins[k])) die("neptune_rt_field_alloc");
+    if (neptune_rt_field_upload(ins[k], in_host[k])) die("neptune_rt_field_upload");
+  }
+  neptune_rt_field *out = nullptr;
+  if (neptune_rt_field_alloc(c, d->dtype, d->rank, d->out_lb, d->out_ub, &out)) die("neptune_rt_field_alloc");
+  if (neptune_rt_apply(s, n_in, ins.data(), out)) die("neptune_rt_apply");
+  if (neptune_rt_field_download(out, out_host)) die("neptune_rt_field_download");
+  if (neptune_rt_sync(c)) die("neptune_rt_sync");
+  for (auto *f : ins) neptune_rt_field_free(f);
+  neptune_rt_field_free(out);
+  neptune_rt_stencil_destroy(s);
+}

@@ -1,0 +1,26 @@
+import os
+import sys
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+
+def pytest_configure(config):
+    config.addinivalue_line("markers", "gpu: needs a CUDA device (run on the B200 box with -m gpu)")
+
+
+@pytest.fixture(scope="session")
+def nb():
+    import neptune_pde_solver_b200 as m
+    m.lib()  # fails loudly if the CUDA library is not built
+    return m
+
+
+@pytest.fixture(scope="session")
+def ctx(nb):
+    c = nb.Context(0)
+    yield c
+    c.close()

@@ -1,0 +1,147 @@
+"""CPU tests of the host logic: the C++ NeptuneIR front end, the body recogniser, the pipeline
+plan and the slab index algebra — all through the C ABI, no GPU needed."""
+import numpy as np
+import pytest
+
+import helpers as H
+from oracle import mlir_subset as ms
+
+CASES = [(n, r, ty) for (n, r, tys) in H.CATALOGUE for ty in tys]
+SMALL = {1: (64,), 2: (20, 28), 3: (9, 12, 14)}
+OPNAME = {0: "access", 1: "constant", 2: "addf", 3: "subf", 4: "mulf", 5: "divf", 6: "negf"}
+
+
+@pytest.mark.parametrize("name,rank,ty", CASES, ids=["%s-%dd-%s" % c for c in CASES])
+def test_cxx_front_end_matches_oracle_parser(nb, name, rank, ty):
+    """Two independent parsers (C++ product, Python oracle) must read the same apply."""
+    text, n_extra = H.program(name, list(SMALL[rank]), ty, lb=None if name == "laplacian_s_1d" else [3] * rank)
+    m = nb.Module(text)
+    assert m.apply_count() == 1
+    d = m.apply_desc(0)
+    ap = [o for o in ms.parse(text).functions["@entry"].ops if o.name == "apply"][0].apply
+    assert d.rank == rank and d.n_inputs == 1 + n_extra and d.dtype == (nb.F64 if ty == "f64" else nb.F32)
+    assert tuple(d.lb) == ap.bounds.lb and tuple(d.ub) == ap.bounds.ub
+    assert tuple(d.out_lb) == ap.out_type.bounds.lb and tuple(d.out_ub) == ap.out_type.bounds.ub
+    assert len(d.ops) == len(ap.body)
+    names = {o.result: i for i, o in enumerate(ap.body)}
+    args = {n: k for k, n in enumerate(ap.input_args)}
+    for o, p in zip(d.ops, ap.body):
+        assert OPNAME[o["opcode"]] == p.name
+        if p.name == "access":
+            assert o["input"] == args[p.operands[0]] and tuple(o["offset"]) == p.offsets
+        elif p.name == "constant":
+            assert o["value"] == float(H.NPT[ty](p.value))
+        else:
+            assert [o["a"], o["b"]][:len(p.operands)] == [names[x] for x in p.operands]
+    assert d.yield_value == names[ap.yield_value]
+    assert nb.body_compiled(d.key()), "catalogue body has no compiled kernel"
+    m.destroy()
+
+
+def test_body_key_ignores_constants_and_extents(nb):
+    a = nb.Module(H.mb.heat_star([8, 8, 8], 0.1)).apply_desc(0).key()
+    b = nb.Module(H.mb.heat_star([64, 32, 16], 0.05, lb=[1, 2, 3])).apply_desc(0).key()
+    c = nb.Module(H.mb.heat_star([8, 8, 8], 0.1, "f32")).apply_desc(0).key()
+    d = nb.Module(H.mb.jacobi_star([8, 8, 8], 0.1)).apply_desc(0).key()
+    assert a == b and a != c and a != d
+
+
+def test_plan_fuses_store_and_skips_uploads(nb):
+    m = nb.Module(H.mb.heat_star([8, 8, 8], 0.1))
+    plan = m.plan("@entry")
+    assert "store fused" in plan and "elided" in plan
+    assert "arg 0 %out: no upload, download" in plan
+    assert "arg 1 %in: upload, no download" in plan
+    assert m.arg_count("@entry") == 2 and m.arg_numel("@entry", 0) == 512
+    src = m.cuda_source(0)
+    assert "A::mul(" in src and "tap<0, -1, 0, 0>" in src
+    m.destroy()
+
+
+BAD = {
+    "index-dependent body": ("""%c = neptune_ir.access %a0[0] : !temp -> f64
+        %x = arith.index_cast %i0 : index to i64""", "EUNSUPPORTED"),
+    "control flow": ("""%c = neptune_ir.access %a0[0] : !temp -> f64
+        %x = scf.if %c -> (f64) { scf.yield %c : f64 } else { scf.yield %c : f64 }""", "EUNSUPPORTED"),
+    "undefined value": ("""%c = arith.addf %nope, %nope : f64""", "EINVAL"),
+}
+
+
+@pytest.mark.parametrize("what", sorted(BAD))
+def test_rejected_bodies(nb, what):
+    body, code = BAD[what]
+    text = """
+#b = #neptune_ir.bounds<lb = [0], ub = [16]>
+!temp = !neptune_ir.temp<element = f64, bounds = #b, location = #neptune_ir.location<"cell">>
+func.func @entry(%%u: !temp) -> !temp {
+  %%r = neptune_ir.apply(%%u) attributes {bounds = #neptune_ir.bounds<lb = [1], ub = [15]>} : (!temp) -> !temp {
+    ^bb0(%%i0: index, %%a0: !temp):
+        %s
+        neptune_ir.yield %%c : f64
+  }
+  func.return %%r : !temp
+}""" % body
+    with pytest.raises(nb.NeptuneError) as e:
+        nb.Module(text)
+    assert code in str(e.value)
+
+
+def test_verifier_rules(nb):
+    """ApplyOp::verify (lib/Dialect/NeptuneIR/NeptuneIRVerifier.cpp:141-171): block args = rank
+    index args + one arg per input — the reference's stale one-index-arg form is rejected."""
+    good = H.mb.heat_star([8, 8], 0.2)
+    stale = good.replace("^bb0(%i0: index, %i1: index, %a0: !temp):", "^bb0(%i0: index, %a0: !temp):")
+    with pytest.raises(nb.NeptuneError) as e:
+        nb.Module(stale)
+    assert "block arg count" in str(e.value)
+    # taps that leave the input box over the apply bounds (UB in the reference) are diagnosed
+    oob = good.replace("lb = [1, 1], ub = [7, 7]", "lb = [0, 1], ub = [7, 7]")
+    with pytest.raises(nb.NeptuneError) as e:
+        nb.Module(oob)
+    assert "outside the input's bounds" in str(e.value)
+    # the reference's CPU pipeline name is not served by this library
+    with pytest.raises(nb.NeptuneError):
+        nb.Module(good, "neptuneir-to-llvm")
+    nb.Module(good, "neptuneir-to-b200{fma=true}").destroy()
+
+
+def test_stencil_shape_attribute_is_cross_checked(nb):
+    ok = H.mb.heat_star([8, 8, 8], 0.1, with_shape_attr=True)
+    nb.Module(ok).destroy()
+    bad = ok.replace("array<i64: 0, 0, 1>", "array<i64: 0, 0, 2>")
+    with pytest.raises(nb.NeptuneError) as e:
+        nb.Module(bad)
+    assert "stencil_shape" in str(e.value)
+
+
+def test_slab_partition_and_localize(nb):
+    from neptune_pde_solver_b200.slab import Slab
+    for n0, nr in [(16, 1), (16, 2), (17, 4), (512, 8), (5, 5)]:
+        rows = [nb.slab_partition(n0, nr, r) for r in range(nr)]
+        assert rows[0][0] == 0 and rows[-1][1] == n0
+        assert all(rows[i][1] == rows[i + 1][0] for i in range(nr - 1))
+        assert max(e - b for b, e in rows) - min(e - b for b, e in rows) <= 1
+    g = nb.Module(H.mb.heat_star([16, 8, 8], 0.1, lb=[10, 0, 0])).apply_desc(0)
+    covered = []
+    for r in range(4):
+        s = Slab(g, 4, r)
+        l = s.local
+        assert l.out_lb[0] == max(10, 10 + s.begin - 1) and l.out_ub[0] == min(26, 10 + s.end + 1)
+        assert l.in_lb[0] == l.out_lb and l.in_ub[0] == l.out_ub
+        assert l.lb[1:] == g.lb[1:] and l.ub[1:] == g.ub[1:]
+        covered += list(range(l.lb[0], l.ub[0]))
+        # the localized apply is the builder's own interior of the local box (halo == radius)
+        again = nb.Module(H.mb.heat_star(list(s.local_shape((16, 8, 8))), 0.1, lb=[l.out_lb[0], 0, 0])).apply_desc(0)
+        assert (again.lb, again.ub, again.out_lb, again.out_ub) == (l.lb, l.ub, l.out_lb, l.out_ub)
+    assert covered == list(range(g.lb[0], g.ub[0]))      # every interior plane swept exactly once
+    with pytest.raises(nb.NeptuneError):
+        nb.slab_localize(g, 4, 0, 0)                       # halo narrower than the radius
+
+
+def test_no_gpu_means_loud_failure(nb):
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present")
+    with pytest.raises(nb.NeptuneError) as e:
+        nb.Context(0)
+    assert "no CPU fallback" in str(e.value)

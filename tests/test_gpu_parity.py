@@ -1,0 +1,287 @@
+"""GPU parity tests: the sm_100a path, called through the C ABI (ctypes over libneptune_rt_b200.so),
+against the CPU oracle (oracle/numpy_lowering.py, a restatement of
+lib/Passes/DataflowLowering.cpp:258-448) on the same seeded inputs.
+
+Tolerance: the default pipeline keeps the body's op order and never contracts, so every comparison
+here is BIT-EXACT (fp64 and fp32).  Only `neptuneir-to-b200{fma=true}` is compared with a
+tolerance: 1e-12 relative max-norm (fp64), as BASELINE.json's north star states.
+"""
+import numpy as np
+import pytest
+
+import helpers as H
+
+pytestmark = pytest.mark.gpu
+
+SHAPES = {  # rank -> (TMA-eligible extents, ragged extents that force the direct kernel)
+    1: [(1000,), (37,)],
+    2: [(96, 160), (45, 51)],
+    3: [(40, 48, 64), (13, 21, 19)],
+}
+
+CASES = [(n, r, ty) for (n, r, tys) in H.CATALOGUE for ty in tys]
+
+
+def _run_entry(nb, ctx, text, u, extra, variant=None):
+    m = nb.Module(text)
+    try:
+        if variant is not None:
+            m.stencil(ctx, 0).set("variant", variant)
+        out = np.full_like(u, np.nan)
+        m.run(ctx, "@entry", [out, u] + list(extra))
+        used = m.stencil(ctx, 0).variant()
+        return out, used
+    finally:
+        m.destroy()
+
+
+@pytest.mark.parametrize("name,rank,ty", CASES, ids=["%s-%dd-%s" % c for c in CASES])
+def test_entry_bit_exact_every_variant(nb, ctx, name, rank, ty):
+    """One call of @entry(out, in, coef...) == the oracle, for every compiled kernel variant."""
+    for si, shape in enumerate(SHAPES[rank]):
+        text, n_extra = H.program(name, list(shape), ty)
+        u, extra = H.inputs(shape, n_extra, ty, seed=1000 + 7 * rank + si)
+        want = H.oracle_entry(text, u, extra)
+        m = nb.Module(text)
+        variants = m.stencil(ctx, 0).variants()
+        m.destroy()
+        assert "direct" in variants
+        out, used = _run_entry(nb, ctx, text, u, extra)
+        assert H.bits_equal(out, want), "auto variant %s differs on %s" % (used, shape)
+        if si == 0 and rank >= 2:
+            assert used.startswith("tma"), "aligned %d-D extents should take the TMA kernel, took %r" % (rank, used)
+        for v in variants:
+            if v.startswith("tma") and si == 1:
+                continue  # ragged rows are not TMA-eligible (checked in test_errors)
+            out, used = _run_entry(nb, ctx, text, u, extra, variant=v)
+            assert used == v
+            assert H.bits_equal(out, want), "variant %s differs on %s" % (v, shape)
+
+
+@pytest.mark.parametrize("name,shape,lb", [
+    ("heat_star", (24, 32, 40), (5, -3, 100)),
+    ("heat_box_2d9", (64, 72), (-7, 9)),
+    ("varcoef_3d7", (12, 16, 24), (1, 2, 3)),
+    ("heat_star", (50,), (11,)),
+])
+def test_nonzero_lower_bounds(nb, ctx, name, shape, lb):
+    """Logical coordinates that do not start at 0: iv + off - inLb (DataflowLowering.cpp:400-404)."""
+    text, n_extra = H.program(name, list(shape), "f64", list(lb))
+    u, extra = H.inputs(shape, n_extra, "f64", seed=77)
+    out, _ = _run_entry(nb, ctx, text, u, extra)
+    assert H.bits_equal(out, H.oracle_entry(text, u, extra))
+
+
+def test_copy_through_shell(nb, ctx):
+    """Points of the result outside `bounds` carry input 0 (memref.copy, DataflowLowering.cpp:282-287)."""
+    text, _ = H.program("heat_star", [20, 24, 32])
+    u, _ = H.inputs((20, 24, 32), 0, "f64", seed=5)
+    out, _ = _run_entry(nb, ctx, text, u, [])
+    shell = np.ones(u.shape, bool)
+    shell[1:-1, 1:-1, 1:-1] = False
+    assert H.bits_equal(out[shell], u[shell])
+    assert not np.array_equal(out[~shell], u[~shell])
+
+
+@pytest.mark.parametrize("name,shape,ty,steps", [
+    ("heat_star", (32, 40, 64), "f64", 25),
+    ("heat_star", (64, 128), "f64", 40),
+    ("heat_box_2d9", (72, 96), "f64", 30),
+    ("jacobi_star", (24, 32, 48), "f64", 30),
+    ("jacobi_star", (24, 32, 48), "f32", 30),
+    ("weighted_3d27", (20, 24, 32), "f64", 10),
+    ("varcoef_3d27", (16, 16, 32), "f64", 6),
+    ("heat_star", (300,), "f64", 100),
+])
+def test_time_loop_bit_exact(nb, ctx, name, shape, ty, steps):
+    """N steps of the host time loop (call entry, swap) stay bit-identical to the oracle."""
+    text, n_extra = H.program(name, list(shape), ty)
+    u, extra = H.inputs(shape, n_extra, ty, seed=31)
+    want = H.oracle_steps(text, u, extra, steps)
+    m = nb.Module(text)
+    try:
+        a, b = u.copy(), np.zeros_like(u)
+        res = m.run_steps(ctx, "@entry", [b, a] + extra, steps)
+        got = [b, a][res]
+        assert res == (0 if steps % 2 else 1)
+        assert H.bits_equal(got, want)
+        # the same loop through neptune_rt_run_steps on device fields
+        st = m.stencil(ctx, 0)
+        fa, fb = nb.Field.from_numpy(ctx, u), nb.Field.from_numpy(ctx, u)
+        fx = [nb.Field.from_numpy(ctx, e) for e in extra]
+        r = st.run_steps(fa, fb, fx, steps)
+        assert H.bits_equal(r.download(), want)
+        for f in [fa, fb] + fx:
+            f.free()
+    finally:
+        m.destroy()
+
+
+def test_apply_planes_partition(nb, ctx):
+    """Sweeping dim-0 plane ranges one by one writes exactly what one whole sweep writes."""
+    shape = (30, 32, 64)
+    text, _ = H.program("heat_star", list(shape))
+    u, _ = H.inputs(shape, 0, "f64", seed=9)
+    want = H.oracle_entry(text, u, [])
+    m = nb.Module(text)
+    try:
+        st = m.stencil(ctx, 0)
+        for variant in st.variants():
+            st.set("variant", variant)
+            fin = nb.Field.from_numpy(ctx, u)
+            fout = nb.Field(ctx, np.float64, [0, 0, 0], list(shape))
+            fout.fill(float("nan"))
+            for p0, p1 in [(0, 1), (1, 7), (7, 8), (8, 29), (29, 30)]:
+                st.apply([fin], fout, planes=(p0, p1))
+            assert H.bits_equal(fout.download(), want), variant
+            fin.free(); fout.free()
+    finally:
+        m.destroy()
+
+
+OPDEF_PROGRAM = """
+#loc = #neptune_ir.location<"cell">
+#b   = #neptune_ir.bounds<lb = [0, 0], ub = [48, 64]>
+#bi  = #neptune_ir.bounds<lb = [1, 1], ub = [47, 63]>
+!temp  = !neptune_ir.temp<element = f64, bounds = #b, location = #loc>
+!field = !neptune_ir.field<element = f64, bounds = #b, location = #loc>
+
+module {
+  // operator definition + call, as in test/smoke_tests/smoke_time_advance.mlir:9-31
+  neptune_ir.linear_opdef @A : (!temp) -> !temp {
+  ^bb0(%x: !temp):
+    %r = neptune_ir.apply(%x) attributes {bounds = #bi} : (!temp) -> !temp {
+      ^bb0(%i: index, %j: index, %a0: !temp):
+        %c = neptune_ir.access %a0[0, 0] : !temp -> f64
+        %n0 = neptune_ir.access %a0[-1, 0] : !temp -> f64
+        %n1 = neptune_ir.access %a0[1, 0] : !temp -> f64
+        %n2 = neptune_ir.access %a0[0, -1] : !temp -> f64
+        %n3 = neptune_ir.access %a0[0, 1] : !temp -> f64
+        %k = arith.constant 4.0 : f64
+        %alpha = arith.constant 0.125 : f64
+        %t0 = arith.mulf %k, %c : f64
+        %t1 = arith.subf %n0, %t0 : f64
+        %t2 = arith.addf %t1, %n1 : f64
+        %t3 = arith.addf %t2, %n2 : f64
+        %t4 = arith.addf %t3, %n3 : f64
+        %lap = arith.mulf %alpha, %t4 : f64
+        %o = arith.addf %c, %lap : f64
+        neptune_ir.yield %o : f64
+    }
+    neptune_ir.return %r : !temp
+  }
+  func.func @entry(%out: memref<?x?xf64>, %in: memref<?x?xf64>) -> memref<?x?xf64> {
+    %fout = neptune_ir.wrap %out : memref<?x?xf64> -> !field
+    %fin  = neptune_ir.wrap %in  : memref<?x?xf64> -> !field
+    %u0   = neptune_ir.load %fin : !field -> !temp
+    %u1 = neptune_ir.apply_linear @A(%u0) : (!temp) -> !temp
+    %u2 = neptune_ir.apply_linear @A(%u1) : (!temp) -> !temp
+    %u3 = neptune_ir.apply_linear @A(%u2) : (!temp) -> !temp
+    neptune_ir.store %u3 to %fout {bounds = #neptune_ir.bounds<lb = [4, 8], ub = [40, 56]>} : !temp to !field
+    %res = neptune_ir.unwrap %fout : !field -> memref<?x?xf64>
+    func.return %res : memref<?x?xf64>
+  }
+}
+"""
+
+
+def test_opdef_calls_and_bounded_store(nb, ctx):
+    """linear_opdef + apply_linear chains (StructureLowering.cpp:31-140) and `store` with bounds
+    (DataflowLowering.cpp:181-218): the destination keeps its old contents outside the box."""
+    from oracle import mlir_subset as ms, numpy_lowering as onp
+    u, _ = H.inputs((48, 64), 0, "f64", seed=3)
+    out0 = np.random.default_rng(4).uniform(-1, 1, size=u.shape)
+    want = out0.copy()
+    onp.run_function(ms.parse(OPDEF_PROGRAM), "@entry", [want, u.copy()])
+    m = nb.Module(OPDEF_PROGRAM)
+    try:
+        assert m.apply_count() == 1 and m.apply_function(0) == "@A"
+        got = out0.copy()
+        m.run(ctx, "@entry", [got, u.copy()])
+        assert H.bits_equal(got, want)
+    finally:
+        m.destroy()
+
+
+def test_fma_pipeline_within_tolerance(nb, ctx):
+    """`neptuneir-to-b200{fma=true}` may contract a*b+c: <= 1e-12 relative max-norm after N steps."""
+    shape, steps = (32, 40, 64), 50
+    text, _ = H.program("heat_star", list(shape))
+    u, _ = H.inputs(shape, 0, "f64", seed=12)
+    want = H.oracle_steps(text, u, [], steps)
+    m = nb.Module(text, "neptuneir-to-b200{fma=true}")
+    try:
+        a, b = u.copy(), np.zeros_like(u)
+        res = m.run_steps(ctx, "@entry", [b, a], steps)
+        got = [b, a][res]
+        rel = np.max(np.abs(got - want)) / np.max(np.abs(want))
+        assert rel <= 1e-12, rel
+    finally:
+        m.destroy()
+
+
+def test_known_answers_on_device(nb, ctx):
+    """Analytic checks that need no oracle: a constant field is a fixed point of the heat step;
+    the 7-point Laplacian of x^2+y^2+z^2 on an integer grid is exactly 6."""
+    shape = (16, 24, 32)
+    text, _ = H.program("heat_star", list(shape))
+    u = np.full(shape, 1.0)
+    out, _ = _run_entry(nb, ctx, text, u, [])
+    assert np.array_equal(out, u)
+    lap = H.mb.weighted_const(list(shape), H.STAR7, [-6.0, 1.0, 1.0, 1.0, 1.0, 1.0, 1.0])
+    z, y, x = np.meshgrid(*[np.arange(n, dtype=np.float64) for n in shape], indexing="ij")
+    q = z * z + y * y + x * x
+    out, _ = _run_entry(nb, ctx, lap, q, [])
+    assert np.array_equal(out[1:-1, 1:-1, 1:-1], np.full((14, 22, 30), 6.0))
+
+
+def test_errors_are_loud(nb, ctx):
+    # a body that is not in the compiled catalogue: EUNSUPPORTED, never a CPU fallback
+    text = H.mb.weighted_const([16, 16], [(0, 0), (0, 2), (2, 0)], [0.5, 0.25, 0.25])
+    m = nb.Module(text)     # recognised (it is a legal linear body) ...
+    with pytest.raises(nb.NeptuneError) as e:
+        m.run(ctx, "@entry", [np.zeros((16, 16)), np.zeros((16, 16))])
+    assert e.value.code == nb.runtime.EUNSUPPORTED and "catalogue" in str(e.value)
+    m.destroy()
+    # result aliasing an input
+    text, _ = H.program("heat_star", [8, 8, 8])
+    m = nb.Module(text)
+    st = m.stencil(ctx, 0)
+    f = nb.Field(ctx, np.float64, [0, 0, 0], [8, 8, 8])
+    with pytest.raises(nb.NeptuneError) as e:
+        st.apply([f], f)
+    assert e.value.code == nb.runtime.EINVAL
+    # a field whose bounds are not the apply's operand type
+    g = nb.Field(ctx, np.float64, [0, 0, 0], [8, 8, 9])
+    with pytest.raises(nb.NeptuneError):
+        st.apply([g], f)
+    # ragged rows cannot take a TMA variant when it is forced
+    m2 = nb.Module(H.program("heat_star", [9, 9, 9])[0])
+    st2 = m2.stencil(ctx, 0)
+    tma = [v for v in st2.variants() if v.startswith("tma")][0]
+    st2.set("variant", tma)
+    with pytest.raises(nb.NeptuneError):
+        m2.run(ctx, "@entry", [np.zeros((9, 9, 9)), np.zeros((9, 9, 9))])
+    with pytest.raises(nb.NeptuneError):
+        st2.set("variant", "no-such-kernel")
+    f.free(); g.free(); m.destroy(); m2.destroy()
+
+
+def test_empty_bounds_is_pure_copy(nb, ctx):
+    text, _ = H.program("heat_star", [8, 8, 8])
+    text = text.replace("lb = [1, 1, 1], ub = [7, 7, 7]", "lb = [3, 3, 3], ub = [3, 7, 7]")
+    u, _ = H.inputs((8, 8, 8), 0, "f64", seed=2)
+    out, _ = _run_entry(nb, ctx, text, u, [])
+    assert H.bits_equal(out, u)
+    assert H.bits_equal(out, H.oracle_entry(text, u, []))
+
+
+def test_launch_accounting(nb, ctx):
+    text, _ = H.program("heat_star", [16, 16, 32])
+    m = nb.Module(text)
+    u, _ = H.inputs((16, 16, 32), 0, "f64", seed=2)
+    n0 = ctx.launch_count()
+    a, b = u.copy(), np.zeros_like(u)
+    m.run_steps(ctx, "@entry", [b, a], 7)
+    assert ctx.launch_count() - n0 == 7      # one kernel per sweep: no copy-through or store kernels
+    m.destroy()

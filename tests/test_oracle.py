@@ -1,0 +1,81 @@
+"""CPU tests of the oracle itself (parity unpinned: the reference holds no golden vectors for the
+apply path, SURVEY.md §4/§8c — so the restatement is pinned three ways instead):
+  1. two independent restatements agree bit for bit: numpy whole-array slices vs gcc-compiled
+     scalar loop nest (`-O2 -fno-tree-vectorize -ffp-contract=off`);
+  2. analytic known answers;
+  3. committed golden vectors (tests/golden/, made by tests/golden/make_golden.py) guard against
+     drift of the oracle between rounds.
+"""
+import os
+
+import numpy as np
+import pytest
+
+import helpers as H
+from oracle import c_lowering as oc
+from oracle import mlir_subset as ms
+from oracle import numpy_lowering as onp
+
+SMALL = {1: (64,), 2: (20, 28), 3: (9, 12, 14)}
+CASES = [(n, r, ty) for (n, r, tys) in H.CATALOGUE for ty in tys]
+
+
+@pytest.mark.parametrize("name,rank,ty", CASES, ids=["%s-%dd-%s" % c for c in CASES])
+def test_numpy_and_c_restatements_agree(name, rank, ty):
+    shape = SMALL[rank]
+    text, n_extra = H.program(name, list(shape), ty)
+    u, extra = H.inputs(shape, n_extra, ty, seed=42)
+    want = H.oracle_entry(text, u, extra)
+    cm = oc.CompiledModule(text, tag="t_%s_%dd_%s" % (name, rank, ty))
+    out = np.full_like(u, np.nan)
+    cm.call("@entry", [out, u] + extra)
+    assert H.bits_equal(out, want)
+    # and over a short time loop
+    assert H.bits_equal(cm.run_steps(u, extra, 5), onp.run_steps(ms.parse(text), u, extra, 5))
+
+
+def test_reference_1d_laplacian_by_hand():
+    """The reference's own body (test/smoke_tests/smoke_time_advance.mlir:13-29) at n=16:
+    lap_i = dxinv2 * ((u[i-1] - 2*u[i]) + u[i+1]), ends copied through."""
+    text = H.mb.laplacian_s_1d(16, 100.0)
+    u = np.arange(16, dtype=np.float64) ** 2
+    out = H.oracle_entry(text, u, [])
+    want = u.copy()
+    for i in range(1, 15):
+        want[i] = 100.0 * ((u[i - 1] - 2.0 * u[i]) + u[i + 1])
+    assert np.array_equal(out, want)
+    assert np.all(out[1:15] == 200.0) and out[0] == 0.0 and out[15] == 225.0
+
+
+def test_known_answers():
+    shape = (10, 12, 14)
+    text, _ = H.program("heat_star", list(shape))
+    u = np.full(shape, 1.0)
+    assert np.array_equal(H.oracle_entry(text, u, []), u)           # constant = fixed point
+    lap = H.mb.weighted_const(list(shape), H.STAR7, [-6.0, 1, 1, 1, 1, 1, 1])
+    z, y, x = np.meshgrid(*[np.arange(n, dtype=np.float64) for n in shape], indexing="ij")
+    out = H.oracle_entry(lap, z * z + y * y + x * x, [])
+    assert np.all(out[1:-1, 1:-1, 1:-1] == 6.0)                     # Laplacian of a quadratic
+    # Jacobi fixed point: f = 0, u = const
+    jt, _ = H.program("jacobi_star", [8, 8, 8])
+    u = np.full((8, 8, 8), 3.0)
+    assert np.allclose(H.oracle_entry(jt, u, [np.zeros_like(u)]), u, rtol=0, atol=1e-15)
+
+
+def test_out_of_box_tap_is_an_error():
+    text, _ = H.program("heat_star", [8, 8])
+    bad = text.replace("lb = [1, 1], ub = [7, 7]", "lb = [0, 1], ub = [7, 7]")
+    with pytest.raises(IndexError):
+        H.oracle_entry(bad, np.zeros((8, 8)), [])
+
+
+def test_golden_vectors():
+    gdir = os.path.join(os.path.dirname(__file__), "golden")
+    files = sorted(f for f in os.listdir(gdir) if f.endswith(".npz"))
+    assert files, "no golden vectors committed"
+    for f in files:
+        g = np.load(os.path.join(gdir, f))
+        text = str(g["mlir"])
+        extra = [g["extra%d" % k] for k in range(int(g["n_extra"]))]
+        got = onp.run_steps(ms.parse(text), g["u0"], extra, int(g["steps"]))
+        assert H.bits_equal(got, g["result"]), f
