@@ -1,0 +1,208 @@
+#!/usr/bin/env python
+"""bench.py — throughput of the `neptune_ir.apply` sweep on B200 (BASELINE.json's metric).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference] [--workload c3|c2|c1|c5]
+
+One "step" is one sweep (one time step) of the workload's apply over its grid:
+  c3 (default, the config the metric is quoted on): 3-D 7-point fp64 heat step, 512^3 PER GPU,
+     dim-0 slab decomposition with NCCL halo exchange for N > 1 (weak scaling).
+`value` is whole-job G point-updates/s with the fields resident in HBM; `e2e` is the same metric
+through the reference-facing entry call `@entry(out, in)` on HOST memrefs (pinned), upload and
+download inside the timed region every step.  `roofline` divides the algorithmic bytes of one
+launch (16 B per point-update: one fp64 read + one fp64 write) by the CUDA-event
+duration of that launch; `cpu_baseline` is the oracle's gcc-compiled restatement of the reference
+lowering timed on this box's host cores (1 thread: the reference emits a single-threaded scf.for
+nest).  `--impl reference` runs only that CPU arm.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+import numpy as np  # noqa: E402
+
+METRIC = "Gpoint-updates/s, 3D 7-pt fp64 heat step, 512^3 per GPU"
+UNIT = "Gpoint-updates/s"
+
+WORKLOADS = {
+    # name: (builder, shape per GPU, dtype, alpha, bytes per update, description)
+    "c3": ("heat_star", [512, 512, 512], "f64", 0.1, 16, "3D 7-pt fp64 heat step, 512^3 per GPU (BASELINE configs[2])"),
+    "c2": ("heat_box_2d9", [16384, 16384], "f64", 0.1, 16, "2D 9-pt fp64 heat step, 16384^2 (BASELINE configs[1])"),
+    "c1": ("heat_star", [4096, 4096], "f64", 0.2, 16, "2D 5-pt fp64 heat step, 4096^2 (BASELINE configs[0])"),
+    "c5": ("jacobi_star", [768, 768, 768], "f64", None, 24, "3D 7-pt Jacobi with rhs, 768^3 f64 (BASELINE configs[4], 1 GPU)"),
+    "c5f32": ("jacobi_star", [768, 768, 768], "f32", None, 12, "3D 7-pt Jacobi with rhs, 768^3 f32 (BASELINE configs[4], 1 GPU)"),
+    "tiny": ("heat_star", [64, 64, 128], "f64", 0.1, 16, "3D 7-pt fp64 heat step, 64x64x128 (self-test)"),
+}
+
+
+def program_text(name, shape):
+    from neptune_pde_solver_b200 import mlir_builders as mb
+    kind, _, ty, alpha, _, _ = WORKLOADS[name]
+    if kind == "heat_star":
+        return mb.heat_star(shape, alpha, ty), 0
+    if kind == "heat_box_2d9":
+        return mb.heat_box_2d9(shape, alpha, ty), 0
+    if kind == "jacobi_star":
+        return mb.jacobi_star(shape, 1.0 / (max(shape) ** 2), ty), 1
+    raise KeyError(kind)
+
+
+def synth(shape, ty, seed):
+    """u0 = product of sines + 0.25 U(-1,1), generated plane-block-wise."""
+    dt = np.float64 if ty == "f64" else np.float32
+    rng = np.random.default_rng(seed)
+    u = np.empty(shape, dtype=dt)
+    axes = [np.sin(2 * np.pi * np.arange(n) / n + 0.3) for n in shape]
+    blk = max(1, (1 << 22) // int(np.prod(shape[1:])))
+    for p in range(0, shape[0], blk):
+        q = min(shape[0], p + blk)
+        t = axes[0][p:q]
+        for a in axes[1:]:
+            t = np.multiply.outer(t, a)
+        u[p:q] = (t + 0.25 * rng.uniform(-1, 1, size=t.shape)).astype(dt)
+    return u
+
+
+def interior_points(shape):
+    n = 1
+    for s in shape:
+        n *= (s - 2)
+    return n
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region (B200_PROFILING.md)."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index=0):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append((time.time(), [c.strip() for c in line.split(",")]))
+
+    def stop(self, t0=None, t1=None):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except subprocess.TimeoutExpired:
+            self.proc.kill()
+        rows = [r for (t, r) in self.rows if (t0 is None or t >= t0) and (t1 is None or t <= t1 + 0.2)] or [r for _, r in self.rows]
+        sm, mx, pw, reasons = [], [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in rows:
+            try:
+                sm.append(float(r[0])); mx.append(float(r[1])); pw.append(float(r[2]))
+            except (ValueError, IndexError):
+                continue
+            for k, nme in enumerate(names):
+                if len(r) > 3 + k and r[3 + k].lower().startswith("active"):
+                    reasons.add(nme)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "power_w_max": max(pw) if pw else None, "samples": len(sm), "reasons": sorted(reasons)}
+
+
+# ------------------------------------------------------------------------------------------------
+# CPU arm: the oracle's gcc-compiled restatement of the reference lowering (kind "port")
+# ------------------------------------------------------------------------------------------------
+def cpu_reference_arm(workload, shape, budget_s, min_steps=2, max_steps=50, warmup=1, u=None):
+    """Times `@entry(out, in)` of the faithful lowering (malloc + copy-through + scalar loop nest +
+    store copy, 1 thread) on the same workload; returns (Gupd/s, ms/step, steps timed, cores)."""
+    from oracle import c_lowering
+    text, n_extra = program_text(workload, shape)
+    ty = WORKLOADS[workload][2]
+    cm = c_lowering.CompiledModule(text, tag="bench_" + workload)
+    a = synth(shape, ty, 20260403) if u is None else np.array(u, copy=True)
+    b = np.empty_like(a)
+    extra = [synth(shape, ty, 20260500 + k) for k in range(n_extra)]
+    for _ in range(max(0, warmup)):
+        cm.call("@entry", [b, a] + extra)
+        a, b = b, a
+    t0 = time.perf_counter()
+    cm.call("@entry", [b, a] + extra)
+    a, b = b, a
+    t_one = time.perf_counter() - t0
+    n = int(max(min_steps, min(max_steps, budget_s / max(t_one, 1e-9))))
+    times = [t_one]
+    for _ in range(n - 1):
+        t0 = time.perf_counter()
+        cm.call("@entry", [b, a] + extra)
+        a, b = b, a
+        times.append(time.perf_counter() - t0)
+    sec = float(np.mean(times))
+    return interior_points(shape) / sec / 1e9, sec * 1e3, len(times), 1
+
+
+def cpu_openmp_context(workload, shape, steps=3):
+    """Context only (NOT the reference): ping-pong sweeps, OpenMP over every host core."""
+    from oracle import c_lowering
+    text, n_extra = program_text(workload, shape)
+    ty = WORKLOADS[workload][2]
+    sw = c_lowering.OpenMPSweep(text, tag="bench_omp_" + workload)
+    a = synth(shape, ty, 20260403)
+    b = a.copy()
+    extra = [synth(shape, ty, 20260500 + k) for k in range(n_extra)]
+    sw.sweep(b, [a] + extra)
+    best = 1e30
+    for _ in range(steps):
+        t0 = time.perf_counter()
+        sw.sweep(b, [a] + extra)
+        best = min(best, time.perf_counter() - t0)
+        a, b = b, a
+    return interior_points(shape) / best / 1e9, len(os.sched_getaffinity(0))
+
+
+def run_reference(args):
+    """`--impl reference`: the reference's CPU lowering of the path (oracle port; the reference
+    itself needs MLIR/LLVM 21 and cannot be built on this image), rank 0 only."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    shape = WORKLOADS[args.workload][1]
+    # each "step" = one faithful sweep; K + W bounded so the run ends within a few minutes
+    k = max(1, min(args.steps, 20))
+    w = max(0, min(args.warmup, 2))
+    gups, ms, n, cores = cpu_reference_arm(args.workload, shape, budget_s=1e9, min_steps=k, max_steps=k, warmup=w)
+    line = {
+        "impl": "reference", "metric": METRIC, "value": gups, "unit": UNIT, "n_gpus": args.gpus,
+        "steps": n, "warmup": w, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": WORKLOADS[args.workload][2], "data": "synthetic",
+        "config": {"workload": WORKLOADS[args.workload][5], "grid": shape, "points_per_step": interior_points(shape)},
+        "cpu_baseline": {"value": gups, "unit": UNIT, "cores": cores, "kind": "port",
+                         "sample": "%d full sweeps of the workload grid, gcc -O2 -ffp-contract=off scalar, "
+                                   "incl. per-sweep malloc + copy-through + store copy "
+                                   "(DataflowLowering.cpp:258-448,165-220); reference is single-threaded by construction" % n},
+        "e2e": {"value": gups, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    if args.omp_context:
+        try:
+            og, oc = cpu_openmp_context(args.workload, shape)
+            line["cpu_context_openmp"] = {"value": og, "unit": UNIT, "cores": oc, "note": "NOT the reference: ping-pong, no copies, OpenMP"}
+        except Exception as e:  # context number only
+            line["cpu_context_openmp"] = {"error": str(e)[:200]}
+    print(json.dumps(line), flush=True)
+    return 0
