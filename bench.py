@@ -206,3 +206,247 @@ def run_reference(args):
             line["cpu_context_openmp"] = {"error": str(e)[:200]}
     print(json.dumps(line), flush=True)
     return 0
+
+
+# ------------------------------------------------------------------------------------------------
+# GPU arm
+# ------------------------------------------------------------------------------------------------
+def pinned_like(shape, dtype):
+    """Pinned host buffer (torch is plumbing here: pinned memory + torch.distributed)."""
+    import torch
+    t = torch.empty(tuple(shape), dtype=torch.float64 if dtype == np.float64 else torch.float32, pin_memory=True)
+    return t, t.numpy()
+
+
+def run_b200(args):
+    import torch
+    import torch.distributed as dist
+    import neptune_pde_solver_b200 as nb
+    from neptune_pde_solver_b200.slab import Slab
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus:
+        if world == 1 and args.gpus > 1:
+            raise SystemExit("launch N>1 with torch.distributed.run (one rank per GPU)")
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the B200 path has no CPU fallback (use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+
+    kind, shape1, ty, _, bytes_per_update, descr = WORKLOADS[args.workload]
+    dt = np.float64 if ty == "f64" else np.float32
+    # weak scaling: global grid = (N * n0) x n1 x n2, dim 0 sharded
+    gshape = [shape1[0] * world] + list(shape1[1:])
+    gtext, n_extra = program_text(args.workload, gshape)
+    ctx = nb.Context(local)
+    gdesc = nb.Module(gtext).apply_desc(0)
+    if world > 1:
+        slab = Slab(gdesc, world, rank)
+        lshape = list(slab.local_shape(gshape))
+        from neptune_pde_solver_b200 import mlir_builders as mb  # local program: same body, local bounds
+        ldesc = slab.local
+        uid = [nb.comm_unique_id() if rank == 0 else None]
+        dist.broadcast_object_list(uid, src=0)
+        ctx.comm_init(uid[0], world, rank)
+        stencil = nb.Stencil(ctx, ldesc)
+        lb = ldesc.out_lb
+        ub = ldesc.out_ub
+        own_points = 1
+        for d in range(len(gshape)):
+            own_points *= max(0, ldesc.ub[d] - ldesc.lb[d])
+    else:
+        lshape = gshape
+        mod = nb.Module(gtext)
+        stencil = mod.stencil(ctx, 0)
+        lb, ub = gdesc.out_lb, gdesc.out_ub
+        own_points = interior_points(gshape)
+    if args.variant:
+        stencil.set("variant", args.variant)
+    if args.zchunk:
+        stencil.set("zchunk", args.zchunk)
+
+    u = synth(lshape, ty, 20260403 + rank)
+    fa = nb.Field(ctx, dt, lb, ub)
+    fb = nb.Field(ctx, dt, lb, ub)
+    fa.upload(u)
+    fb.upload(u)   # both ping-pong buffers start with a valid boundary shell
+    extra = []
+    for k in range(n_extra):
+        f = nb.Field(ctx, dt, lb, ub)
+        f.upload(synth(lshape, ty, 20260500 + k + 100 * rank))
+        extra.append(f)
+
+    def barrier():
+        ctx.sync()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- device-resident timing: W warm-up steps, then exactly K steps ---------------------------
+    cur = stencil.run_steps(fa, fb, extra, args.warmup)
+    other = fb if cur is fa else fa
+    barrier()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+        time.sleep(0.25)
+    barrier()
+    n0 = ctx.launch_count()
+    t_wall0 = time.time()
+    ctx.timer_start()
+    cur = stencil.run_steps(cur, other, extra, args.steps)
+    ms = ctx.timer_stop()
+    barrier()
+    t_wall1 = time.time()
+    launches = ctx.launch_count() - n0
+    clocks = sampler.stop(t_wall0, t_wall1) if rank == 0 else None
+    if world > 1:
+        t = torch.tensor([ms, float(own_points), float(launches)], dtype=torch.float64, device="cuda")
+        tmax = t.clone()
+        dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
+        tsum = t.clone()
+        dist.all_reduce(tsum, op=dist.ReduceOp.SUM)
+        ms_max, total_points, launches_all = float(tmax[0]), float(tsum[1]), int(tsum[2])
+    else:
+        ms_max, total_points, launches_all = ms, float(own_points), launches
+    ms_per_step = ms_max / args.steps
+    value = total_points / (ms_per_step * 1e-3) / 1e9
+    variant = stencil.variant()
+
+    # ---- roofline of the dominant kernel: whole-box sweep launches timed with CUDA events on the
+    # launching stream (at N=1 the timed region above IS K such launches, one per step) ------------
+    if world == 1:
+        kernel_ms = ms / max(1, launches)
+    else:
+        ins = [cur] + extra
+        for _ in range(3):
+            stencil.apply(ins, other)
+        ctx.sync()
+        ctx.timer_start()
+        for _ in range(10):
+            stencil.apply(ins, other)
+        kernel_ms = ctx.timer_stop() / 10
+    box_points = own_points
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except (OSError, ValueError):
+        pass
+    peak = float(peaks.get("hbm_gbs", 6650.0))
+    peak_kind = "measured (MEASURED_PEAKS.json hbm_gbs)" if "hbm_gbs" in peaks else "fallback 6650 GB/s (B200_PROFILING.md)"
+    achieved = box_points * bytes_per_update / (kernel_ms * 1e-3) / 1e9
+    roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                "traffic": args.traffic, "peak_kind": peak_kind, "frac_of_8TBps": achieved / 8000.0,
+                "kernel": "sweep_%s<%s>" % (variant.split(":")[0], kind), "kernel_ms": kernel_ms,
+                "algorithmic_bytes_per_launch": box_points * bytes_per_update,
+                "bytes_per_update": bytes_per_update}
+
+    # ---- e2e: the reference-facing entry call on HOST memrefs, copies inside the timed region -----
+    from neptune_pde_solver_b200 import mlir_builders as mb
+    if world > 1:
+        ltext = {"heat_star": lambda: mb.heat_star(lshape, WORKLOADS[args.workload][3], ty, lb),
+                 "heat_box_2d9": lambda: mb.heat_box_2d9(lshape, WORKLOADS[args.workload][3], ty, lb),
+                 "jacobi_star": lambda: mb.jacobi_star(lshape, 1.0 / (max(gshape) ** 2), ty, lb)}[kind]()
+        emod = nb.Module(ltext)
+    else:
+        emod = mod
+    if args.variant:
+        emod.stencil(ctx, 0).set("variant", args.variant)
+    keep = []
+    hargs = []
+    for k in range(2 + n_extra):
+        t, a = pinned_like(lshape, dt)
+        keep.append(t)
+        hargs.append(a)
+    hargs[1][...] = u
+    for k in range(n_extra):
+        hargs[2 + k][...] = synth(lshape, ty, 20260500 + k + 100 * rank)
+    e_steps = max(1, min(args.steps, args.e2e_steps))
+    for _ in range(2):
+        emod.run(ctx, "@entry", hargs)
+    barrier()
+    l0 = ctx.launch_count()
+    t0 = time.perf_counter()
+    for _ in range(e_steps):
+        emod.run(ctx, "@entry", hargs)          # upload inputs, sweep, download result, sync
+        hargs[0], hargs[1] = hargs[1], hargs[0]  # the host time loop's swap
+    barrier()
+    e_sec = time.perf_counter() - t0
+    e_launches = ctx.launch_count() - l0
+    if world > 1:
+        t = torch.tensor([e_sec], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        e_sec = float(t[0])
+    e_value = total_points / (e_sec / e_steps) / 1e9
+    field_bytes = int(np.prod(lshape)) * np.dtype(dt).itemsize
+    e2e = {"value": e_value, "unit": UNIT, "h2d_bytes_per_step": field_bytes * (1 + n_extra) * world,
+           "d2h_bytes_per_step": field_bytes * world, "steps": e_steps, "ms_per_step": e_sec / e_steps * 1e3,
+           "api": "neptune_b200_run_host(@entry(out, in)) on pinned host memrefs, one sweep per call"}
+
+    # ---- CPU baseline (rank 0, N=1 only): bounded sample of the same workload --------------------
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu:
+        cshape = list(shape1)
+        g, cms, n, cores = cpu_reference_arm(args.workload, cshape, budget_s=args.cpu_seconds, min_steps=2, max_steps=40, warmup=1)
+        cpu = {"value": g, "unit": UNIT, "cores": cores, "kind": "port", "ms_per_step": cms,
+               "sample": "%d full sweeps of the %s grid through the oracle's gcc -O2 -ffp-contract=off scalar "
+                         "restatement of DataflowLowering.cpp:258-448 + store copy :165-220 (1 thread: the "
+                         "reference emits no parallel construct)" % (n, "x".join(map(str, cshape)))}
+        if args.omp_context:
+            try:
+                og, oc = cpu_openmp_context(args.workload, cshape)
+                cpu["context_openmp"] = {"value": og, "cores": oc, "note": "NOT the reference: ping-pong, no copies, OpenMP all cores"}
+            except Exception as e:
+                cpu["context_openmp"] = {"error": str(e)[:200]}
+
+    if rank == 0:
+        line = {
+            "metric": METRIC if args.workload == "c3" else "Gpoint-updates/s, " + descr,
+            "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": ty, "data": "synthetic",
+            "config": {"workload": descr, "grid_per_gpu": list(shape1), "global_grid": gshape,
+                       "decomposition": "dim-0 slabs, 1 ghost plane, NCCL send/recv overlapped with interior" if world > 1 else "single domain",
+                       "points_per_step": int(total_points), "kernel_variant": variant,
+                       "l2": "inputs larger than L2 (%.2f GB per field vs 126 MB L2); no flush needed" % (field_bytes / 1e9),
+                       "fma": False, "parity": "bit-exact vs oracle (tests/test_gpu_parity.py)"},
+            "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e,
+            "gpu_launches": int(launches_all), "e2e_gpu_launches": int(e_launches), "clocks": clocks,
+            "achieved_GBps_step": total_points * bytes_per_update / (ms_per_step * 1e-3) / 1e9 / world,
+        }
+        print(json.dumps(line), flush=True)
+    for f in [fa, fb] + extra:
+        f.free()
+    ctx.close()
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=100)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default="c3", choices=sorted(WORKLOADS))
+    ap.add_argument("--variant", default="")
+    ap.add_argument("--zchunk", default="")
+    ap.add_argument("--e2e-steps", type=int, default=10)
+    ap.add_argument("--cpu-seconds", type=float, default=12.0)
+    ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--omp-context", action="store_true")
+    ap.add_argument("--traffic", type=float, default=None,
+                    help="dram bytes per launch from the committed ncu --set full capture (profiles/)")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
+    if args.impl == "reference":
+        return run_reference(args)
+    return run_b200(args)
+
+
+if __name__ == "__main__":
+    sys.exit(main())
