@@ -90,7 +90,7 @@ class ClockSampler:
     def start(self):
         try:
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
-                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                          "--format=csv,noheader,nounits", "-lms", "20"],
                                          stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.thread = threading.Thread(target=self._read, daemon=True)
             self.thread.start()
@@ -265,7 +265,7 @@ def run_b200(args):
         own_points = interior_points(gshape)
     if args.variant:
         stencil.set("variant", args.variant)
-    if args.zchunk:
+    if args.zchunk and args.zchunk != "0":
         stencil.set("zchunk", args.zchunk)
 
     u = synth(lshape, ty, 20260403 + rank)

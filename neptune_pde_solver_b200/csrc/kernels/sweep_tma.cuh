@@ -6,8 +6,9 @@
 //     (TX + 2*HX) x (TY + 2*RY) x 1 elements including its x/y halo, completion signalled on an
 //     mbarrier (no thread ever issues a global load for it, out-of-box halo elements are
 //     zero-filled by the TMA unit and never feed an in-bounds point);
-//   * a ring of NS such stages lets the TMA unit run NS - 2*RZ - 1 planes ahead of the math, which
-//     is what keeps enough bytes in flight to cover HBM latency at ~6.5 TB/s;
+//   * a ring of NS such stages, filled by a dedicated producer warp (one elected thread) and
+//     handed back by the consumer warps through full[]/empty[] mbarriers — no CTA-wide barrier in
+//     the steady state — lets the TMA unit run NS - 2*RZ - 1 planes ahead of the math;
 //   * inputs read only at offset 0 (coefficient fields, right-hand sides) stream straight from
 //     global memory with 128-bit read-only loads; results leave with 128-bit stores.
 // Work decomposition
@@ -29,8 +30,9 @@
 
 namespace neptune {
 
-template <int TX_, int TY_, int VY_, int NS_, int MINB_> struct TileCfg {
+template <int TX_, int TY_, int VY_, int NS_, int MINB_, bool STREAM_ = false> struct TileCfg {
   static constexpr int TX = TX_, TY = TY_, VY = VY_, NS = NS_, MINB = MINB_;
+  static constexpr bool STREAM = STREAM_;  // results leave with st.global.cs (evict-first in L2)
 };
 
 template <class F, class C> struct TmaGeom {
@@ -44,13 +46,14 @@ template <class F, class C> struct TmaGeom {
   static constexpr int STAGE_TX_BYTES = SXP * SY * S;               // bytes one TMA box delivers
   static constexpr int STAGE_BYTES = (STAGE_TX_BYTES + 127) / 128 * 128;
   static constexpr int NTX = C::TX / VX, NTY = C::TY / C::VY;
-  static constexpr int THREADS = NTX * NTY;
+  static constexpr int CONSUMERS = NTX * NTY;        // math threads
+  static constexpr int THREADS = CONSUMERS + 32;     // + one producer warp
   static constexpr int NS = C::NS;
-  static constexpr int SMEM_BYTES = NS * STAGE_BYTES + NS * 8 + 128;  // + barriers + alignment slack
+  static constexpr int SMEM_BYTES = NS * STAGE_BYTES + 2 * NS * 8 + 128;  // + full/empty barriers + alignment slack
   static_assert(NS >= 2 * RZ + 2, "ring must hold the z window plus one plane in flight");
   static_assert(C::TX % VX == 0 && C::TY % C::VY == 0, "tile must be a multiple of the thread tile");
   static_assert(SXP <= 256 && SY <= 256, "TMA box dimensions are limited to 256 elements");
-  static_assert(THREADS % 32 == 0 && THREADS <= 1024, "bad thread count");
+  static_assert(CONSUMERS % 32 == 0 && THREADS <= 1024, "bad thread count");
 };
 
 __device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -60,6 +63,9 @@ __device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
 }
 __device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
   asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
 }
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
   uint32_t done;
@@ -100,12 +106,13 @@ template <class T, int VX> __device__ __forceinline__ void ldg_vec(T (&dst)[VX],
 #pragma unroll
   for (int i = 0; i < VX; ++i) dst[i] = u.e[i];
 }
-template <class T, int VX> __device__ __forceinline__ void stg_vec(T *dst, const T (&src)[VX]) {
+template <class T, int VX, bool STREAM> __device__ __forceinline__ void stg_vec(T *dst, const T (&src)[VX]) {
   typedef typename Vec16<T>::type V;
   union { V v; T e[VX]; } u;
 #pragma unroll
   for (int i = 0; i < VX; ++i) u.e[i] = src[i];
-  *reinterpret_cast<V *>(dst) = u.v;
+  if constexpr (STREAM) __stcs(reinterpret_cast<V *>(dst), u.v);
+  else *reinterpret_cast<V *>(dst) = u.v;
 }
 
 // register window accessor for thread-tile point (IY, IX)
@@ -131,18 +138,20 @@ sweep_tma(const __grid_constant__ KParams<F> p, const __grid_constant__ CUtensor
   typedef typename F::T T;
   constexpr int RZ = G::RZ, RY = G::RY, RX = G::RX, HX = G::HX, VX = G::VX, VY = C::VY, NS = G::NS;
   constexpr int NPW = F::NIN > 1 ? F::NIN - 1 : 1;
+  constexpr int NCW = G::CONSUMERS / 32;  // consumer warps
 
   extern __shared__ __align__(128) unsigned char smem_raw[];
   unsigned char *smem = reinterpret_cast<unsigned char *>((reinterpret_cast<uintptr_t>(smem_raw) + 127) & ~uintptr_t(127));
-  const uint32_t bar0 = smem_u32(smem + NS * G::STAGE_BYTES);
+  const uint32_t full0 = smem_u32(smem + NS * G::STAGE_BYTES);  // full[s]: TMA bytes of stage s have landed
+  const uint32_t empty0 = full0 + 8 * NS;                       // empty[s]: every consumer warp is done with stage s
   const uint32_t stage0 = smem_u32(smem);
 
   const int tid = threadIdx.x;
-  const int tx = tid % G::NTX, ty = tid / G::NTX;
-  const int lx = tx * VX, ly = ty * VY;  // tile-local origin of this thread's points
-
   if (tid == 0) {
-    for (int s = 0; s < NS; ++s) mbar_init(bar0 + 8 * s, 1);
+    for (int s = 0; s < NS; ++s) {
+      mbar_init(full0 + 8 * s, 1);
+      mbar_init(empty0 + 8 * s, NCW);
+    }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   __syncthreads();
@@ -158,24 +167,31 @@ sweep_tma(const __grid_constant__ KParams<F> p, const __grid_constant__ CUtensor
     x0 = (p.cxo + cx) * C::TX;
   };
 
-  // ---- producer: thread 0 streams plane-tiles into the ring ----------------------------------
-  int p_item = blockIdx.x, p_j = 0;
-  unsigned p_count = 0;
-  auto issue = [&]() {
-    if (p_item >= p.nitems) return;
-    int zb, ze, y0, x0;
-    geom(p_item, zb, ze, y0, x0);
-    const unsigned s = p_count % NS;
-    mbar_expect_tx(bar0 + 8 * s, G::STAGE_TX_BYTES);
-    tma_load_3d(stage0 + s * G::STAGE_BYTES, &tmap, x0 - HX, y0 - RY, zb - RZ + p_j, bar0 + 8 * s);
-    ++p_count;
-    if (++p_j == ze - zb + 2 * RZ) { p_j = 0; p_item += gridDim.x; }
-  };
-  if (tid == 0) {
-    for (int s = 0; s < NS; ++s) issue();
+  if (tid >= G::CONSUMERS) {
+    // ---- producer warp: one elected thread streams plane-tiles into the ring, gated only by the
+    // empty barriers, so loads run up to NS planes ahead of the math and never wait for a CTA-wide
+    // barrier ----------------------------------------------------------------------------------------
+    if (tid == G::CONSUMERS) {
+      unsigned n = 0;
+      for (int item = blockIdx.x; item < p.nitems; item += gridDim.x) {
+        int zb, ze, y0, x0;
+        geom(item, zb, ze, y0, x0);
+        const int nslots = ze - zb + 2 * RZ;
+        for (int j = 0; j < nslots; ++j, ++n) {
+          const unsigned s = n % NS;
+          mbar_wait(empty0 + 8 * s, ((n / NS) & 1) ^ 1);  // fresh barrier: the wait on the previous phase passes
+          mbar_expect_tx(full0 + 8 * s, G::STAGE_TX_BYTES);
+          tma_load_3d(stage0 + s * G::STAGE_BYTES, &tmap, x0 - HX, y0 - RY, zb - RZ + j, full0 + 8 * s);
+        }
+      }
+    }
+    return;
   }
 
-  // ---- consumers --------------------------------------------------------------------------------
+  // ---- consumer warps ---------------------------------------------------------------------------
+  const int tx = tid % G::NTX, ty = tid / G::NTX;
+  const int lx = tx * VX, ly = ty * VY;  // tile-local origin of this thread's points
+  const bool lane0 = (tid & 31) == 0;
   unsigned n = 0;  // slots consumed so far
   for (int item = blockIdx.x; item < p.nitems; item += gridDim.x) {
     int zb, ze, y0, x0;
@@ -212,11 +228,12 @@ sweep_tma(const __grid_constant__ KParams<F> p, const __grid_constant__ CUtensor
         }
       }
 
-      mbar_wait(bar0 + 8 * (n % NS), (n / NS) & 1);
+      mbar_wait(full0 + 8 * (n % NS), (n / NS) & 1);
+      if (!compute) continue;
 
-      if (compute && live) {
-        // register window: planes z-RZ..z+RZ are slots n-2RZ..n
-        T w[2 * RZ + 1][VY + 2 * RY][VX + 2 * RX];
+      // register window: planes z-RZ..z+RZ are slots n-2RZ..n
+      T w[2 * RZ + 1][VY + 2 * RY][VX + 2 * RX];
+      if (live) {
 #pragma unroll
         for (int dz = 0; dz <= 2 * RZ; ++dz) {
           const unsigned s = (n - 2 * RZ + dz) % NS;
@@ -235,6 +252,19 @@ sweep_tma(const __grid_constant__ KParams<F> p, const __grid_constant__ CUtensor
             }
           }
         }
+      }
+      // this warp has its window in registers: hand the oldest stage (plane z-RZ) back to the
+      // producer, and at the end of an item the 2RZ younger ones too (the next item restarts its z window)
+      __syncwarp();
+      if (lane0) {
+        mbar_arrive(empty0 + 8 * ((n - 2 * RZ) % NS));
+        if (j == nslots - 1) {
+#pragma unroll
+          for (int q = 1; q <= 2 * RZ; ++q) mbar_arrive(empty0 + 8 * ((n - 2 * RZ + q) % NS));
+        }
+      }
+
+      if (live) {
         const bool zin = z >= p.blo[0] && z < p.bhi[0];
         static_for<VY>([&](auto iyc) {
           constexpr int IY = decltype(iyc)::value;
@@ -254,7 +284,7 @@ sweep_tma(const __grid_constant__ KParams<F> p, const __grid_constant__ CUtensor
             });
             T *dst = p.out + (long long)z * p.out_sz + (long long)y * p.out_sy + gx;
             if (gx >= p.wlo[2] && gx + VX <= p.whi[2]) {
-              stg_vec<T, VX>(dst, res);
+              stg_vec<T, VX, C::STREAM>(dst, res);
             } else {
 #pragma unroll
               for (int ix = 0; ix < VX; ++ix)
@@ -262,11 +292,6 @@ sweep_tma(const __grid_constant__ KParams<F> p, const __grid_constant__ CUtensor
             }
           }
         });
-      }
-
-      if (n >= 2u * RZ) {
-        __syncthreads();  // every thread is done with slot n - 2RZ: its stage may be overwritten
-        if (tid == 0) issue();
       }
     }
   }
