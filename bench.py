@@ -265,6 +265,8 @@ def run_b200(args):
         own_points = interior_points(gshape)
     if args.variant:
         stencil.set("variant", args.variant)
+    if args.tblock:
+        stencil.set("tblock", args.tblock)
     if args.zchunk and args.zchunk != "0":
         stencil.set("zchunk", args.zchunk)
 
@@ -320,6 +322,7 @@ def run_b200(args):
     # launching stream (at N=1 the timed region above IS K such launches, one per step) ------------
     if world == 1:
         kernel_ms = ms / max(1, launches)
+        steps_per_launch = args.steps / max(1, launches)   # 2 when run_steps used the temporally blocked kernel
     else:
         ins = [cur] + extra
         for _ in range(3):
@@ -329,6 +332,7 @@ def run_b200(args):
         for _ in range(10):
             stencil.apply(ins, other)
         kernel_ms = ctx.timer_stop() / 10
+        steps_per_launch = 1.0
     box_points = own_points
     peaks = {}
     try:
@@ -337,11 +341,12 @@ def run_b200(args):
         pass
     peak = float(peaks.get("hbm_gbs", 6650.0))
     peak_kind = "measured (MEASURED_PEAKS.json hbm_gbs)" if "hbm_gbs" in peaks else "fallback 6650 GB/s (B200_PROFILING.md)"
-    achieved = box_points * bytes_per_update / (kernel_ms * 1e-3) / 1e9
+    achieved = box_points * bytes_per_update * steps_per_launch / (kernel_ms * 1e-3) / 1e9
     roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                 "traffic": args.traffic, "peak_kind": peak_kind, "frac_of_8TBps": achieved / 8000.0,
                 "kernel": "sweep_%s<%s>" % (variant.split(":")[0], kind), "kernel_ms": kernel_ms,
-                "algorithmic_bytes_per_launch": box_points * bytes_per_update,
+                "algorithmic_bytes_per_launch": box_points * bytes_per_update * steps_per_launch,
+                "steps_per_launch": steps_per_launch,
                 "bytes_per_update": bytes_per_update}
 
     # ---- e2e: the reference-facing entry call on HOST memrefs, copies inside the timed region -----
@@ -435,6 +440,7 @@ def main():
     ap.add_argument("--workload", default="c3", choices=sorted(WORKLOADS))
     ap.add_argument("--variant", default="")
     ap.add_argument("--zchunk", default="")
+    ap.add_argument("--tblock", type=int, default=0, help="time steps fused per launch (1 or 2; 0 = library default)")
     ap.add_argument("--e2e-steps", type=int, default=10)
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
     ap.add_argument("--no-cpu", action="store_true")

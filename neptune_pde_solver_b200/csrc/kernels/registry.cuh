@@ -6,6 +6,7 @@
 #include "registry.h"
 #include "sweep_direct.cuh"
 #include "sweep_tma.cuh"
+#include "sweep_tb2.cuh"
 
 namespace neptune {
 
@@ -94,6 +95,58 @@ template <class F, class C, bool FMA> int launch_tma(const SweepArgs &a) {
   return (int)cudaGetLastError();
 }
 
+template <class F, class C, bool FMA> int launch_tb2(const SweepArgs &a) {
+  typedef Tb2Geom<F, C> G;
+  auto kernel = sweep_tb2<F, C, FMA>;
+  static int occ_cached[16] = {0};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (dev < 0 || dev >= 16) dev = 0;
+  if (occ_cached[dev] == 0) {
+    cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, G::SMEM_BYTES);
+    if (e != cudaSuccess) return (int)e;
+    int occ = 0;
+    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kernel, G::THREADS, G::SMEM_BYTES);
+    if (e != cudaSuccess) return (int)e;
+    if (occ < 1) return (int)cudaErrorLaunchOutOfResources;
+    occ_cached[dev] = occ;
+  }
+  if (!a.tmap) return (int)cudaErrorInvalidValue;
+  KParams<F> p;
+  fill_params<F>(p, a);
+  const int wz = a.whi[0] - a.wlo[0];
+  if (wz <= 0 || a.whi[1] <= a.wlo[1] || a.whi[2] <= a.wlo[2]) return 0;
+  p.cxo = a.wlo[2] / C::TX;
+  p.cyo = a.wlo[1] / C::TY;
+  p.ncx = (a.whi[2] + C::TX - 1) / C::TX - p.cxo;
+  p.ncy = (a.whi[1] + C::TY - 1) / C::TY - p.cyo;
+  const int ncols = p.ncx * p.ncy;
+  const int slots = a.sm_count * occ_cached[dev];
+  p.zchunk = a.zchunk > 0 ? std::min(a.zchunk, wz) : choose_zchunk(wz, ncols, slots, 2);
+  p.nchunks = (wz + p.zchunk - 1) / p.zchunk;
+  const long long items = (long long)p.nchunks * ncols;
+  if (items > 0x7fffffffLL) return (int)cudaErrorInvalidConfiguration;
+  p.nitems = (int)items;
+  const int grid = (int)std::min<long long>(items, slots);
+  kernel<<<grid, G::THREADS, G::SMEM_BYTES, a.stream>>>(p, *a.tmap);
+  return (int)cudaGetLastError();
+}
+
+template <class F, class C, bool FMA> Variant tb2_variant(const char *name) {
+  typedef Tb2Geom<F, C> G;
+  Variant v;
+  v.name = name;
+  v.kind = VARIANT_TB2;
+  v.fma = FMA;
+  v.steps = 2;
+  v.tx = C::TX; v.ty = C::TY;
+  v.box_x = G::P0; v.box_y = G::BOX_Y;
+  v.halo_x = 2 * G::VX; v.halo_y = 2;
+  v.threads = G::THREADS; v.smem = G::SMEM_BYTES;
+  v.launch = &launch_tb2<F, C, FMA>;
+  return v;
+}
+
 template <class F, class C, bool FMA> Variant tma_variant(const char *name) {
   typedef TmaGeom<F, C> G;
   Variant v;
@@ -112,6 +165,10 @@ template <class F, class C, bool FMA> Variant tma_variant(const char *name) {
 typedef TileCfg<64, 16, 2, 8, 2> Tile3A;    // r01 sweep on C3: 348 Gupd/s (0.864 of the measured copy peak)
 typedef TileCfg<128, 8, 2, 8, 2> Tile3B;
 typedef TileCfg<128, 16, 4, 5, 2> Tile3C;
+typedef Tb2Cfg<64, 16, 2, 5, 2> Tb2A;       // two time steps per launch (sweep_tb2.cuh)
+typedef Tb2Cfg<64, 16, 2, 7, 1> Tb2B;
+typedef Tb2Cfg<128, 16, 2, 5, 1> Tb2C;
+typedef Tb2Cfg<64, 32, 4, 5, 1> Tb2D;
 typedef TileCfg<64, 8, 1, 6, 1> Tile3W;   // many-input bodies (one coefficient field per tap)
 typedef TileCfg<128, 32, 8, 3, 2> Tile2A;
 typedef TileCfg<128, 16, 4, 4, 2> Tile2B;
@@ -139,6 +196,13 @@ template <class F> struct BodyRegistrar {
         e.variants.push_back(tma_variant<F, Tile3A, true>("tma:64x16"));
         e.variants.push_back(tma_variant<F, Tile3B, false>("tma:128x8"));
         e.variants.push_back(tma_variant<F, Tile3C, false>("tma:128x16"));
+        if constexpr (F::NIN == 1 && F::RZ == 1) {
+          e.variants.push_back(tb2_variant<F, Tb2A, false>("tb2:64x16"));
+          e.variants.push_back(tb2_variant<F, Tb2A, true>("tb2:64x16"));
+          e.variants.push_back(tb2_variant<F, Tb2B, false>("tb2:64x16n7"));
+          e.variants.push_back(tb2_variant<F, Tb2C, false>("tb2:128x16"));
+          e.variants.push_back(tb2_variant<F, Tb2D, false>("tb2:64x32"));
+        }
       } else {
         e.variants.push_back(tma_variant<F, Tile2A, false>("tma:128x32"));
         e.variants.push_back(tma_variant<F, Tile2A, true>("tma:128x32"));

@@ -30,7 +30,7 @@ struct SweepArgs {
   const CUtensorMap *tmap = nullptr;  // tensor map of the staged input (TMA variants)
 };
 
-enum VariantKind { VARIANT_DIRECT = 0, VARIANT_TMA = 1 };
+enum VariantKind { VARIANT_DIRECT = 0, VARIANT_TMA = 1, VARIANT_TB2 = 2 };
 
 struct Variant {
   std::string name;     // "direct", "tma:64x16", ...
@@ -40,6 +40,7 @@ struct Variant {
   int box_x = 0, box_y = 0;     // TMA box incl. halo, elements
   int halo_x = 0, halo_y = 0;   // box origin = tile origin - halo
   int threads = 0, smem = 0;
+  int steps = 1;                // time steps one launch advances (2: temporally blocked)
   int (*launch)(const SweepArgs &) = nullptr;   // returns a cudaError_t
 };
 

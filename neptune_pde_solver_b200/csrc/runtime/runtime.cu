@@ -127,6 +127,7 @@ struct neptune_rt_stencil {
   const BodyEntry *body = nullptr;
   bool fma = false;
   std::string want = "auto";
+  std::string want_tb = "auto";  // which temporally blocked kernel run_steps uses when tblock == 2
   int zchunk = 0;
   int tblock = 1;
   const Variant *last = nullptr;
@@ -451,10 +452,18 @@ extern "C" int neptune_rt_stencil_destroy(neptune_rt_stencil *s) {
 extern "C" int neptune_rt_stencil_set(neptune_rt_stencil *s, const char *key, const char *value) {
   if (!s || !key || !value) return set_error(s ? s->ctx : nullptr, NEPTUNE_RT_EINVAL, "stencil_set: NULL argument");
   const std::string k = key, v = value;
+  if (k == "variant" && v.rfind("tb2:", 0) == 0) {
+    bool found = false;
+    for (auto &var : s->body->variants) found |= var.name == v && var.kind == neptune::VARIANT_TB2;
+    if (!found) return set_error(s->ctx, NEPTUNE_RT_EINVAL, "stencil_set: this body has no temporally blocked kernel '%s'", value);
+    s->want_tb = v;
+    s->tblock = 2;
+    return NEPTUNE_RT_OK;
+  }
   if (k == "variant") {
     if (v != "auto") {
       bool found = false;
-      for (auto &var : s->body->variants) found |= var.name == v;
+      for (auto &var : s->body->variants) found |= var.name == v && var.kind != neptune::VARIANT_TB2;
       if (!found) return set_error(s->ctx, NEPTUNE_RT_EINVAL, "stencil_set: this body has no kernel variant '%s'", value);
     }
     s->want = v;
@@ -463,7 +472,7 @@ extern "C" int neptune_rt_stencil_set(neptune_rt_stencil *s, const char *key, co
   if (k == "zchunk") { s->zchunk = std::max(0, std::atoi(value)); return NEPTUNE_RT_OK; }
   if (k == "tblock") {
     const int t = std::atoi(value);
-    if (t < 1 || t > 8) return set_error(s->ctx, NEPTUNE_RT_EINVAL, "stencil_set: tblock must be 1..8");
+    if (t < 1 || t > 2) return set_error(s->ctx, NEPTUNE_RT_EINVAL, "stencil_set: tblock must be 1 or 2");
     s->tblock = t;
     return NEPTUNE_RT_OK;
   }
@@ -474,14 +483,14 @@ extern "C" int neptune_rt_stencil_set(neptune_rt_stencil *s, const char *key, co
 extern "C" int neptune_rt_stencil_variant_count(neptune_rt_stencil *s) {
   if (!s) return 0;
   int n = 0;
-  for (auto &v : s->body->variants) n += v.fma == false;
+  for (auto &v : s->body->variants) n += v.fma == false && v.kind != neptune::VARIANT_TB2;
   return n;
 }
 extern "C" const char *neptune_rt_stencil_variant_name(neptune_rt_stencil *s, int index) {
   if (!s) return nullptr;
   int n = 0;
   for (auto &v : s->body->variants)
-    if (!v.fma && n++ == index) return v.name.c_str();
+    if (!v.fma && v.kind != neptune::VARIANT_TB2 && n++ == index) return v.name.c_str();
   return nullptr;
 }
 
@@ -534,8 +543,26 @@ bool tma_eligible(const neptune_rt_stencil *s, int n_in, neptune_rt_field *const
   return true;
 }
 
+// The temporally blocked kernel takes: a body with a tb2 kernel, one input sharing the result's box
+// (TMA-eligible), rank 3, and apply bounds at least one point inside the box on every side (so no
+// in-bounds point of either level reads outside the box; the reference's own fixtures obey this).
+bool tb2_eligible(const neptune_rt_stencil *s, neptune_rt_field *a, neptune_rt_field *b) {
+  bool has = false;
+  for (auto &v : s->body->variants) has |= v.kind == neptune::VARIANT_TB2;
+  const neptune_rt_stencil_desc &d = s->desc.c;
+  if (!has || d.rank != 3 || d.n_inputs != 1) return false;
+  neptune_rt_field *in1[1] = {a};
+  if (!tma_eligible(s, 1, in1, b) || encode_tiled() == nullptr) return false;
+  for (int x = 0; x < 3; ++x) {
+    if (d.ub[x] <= d.lb[x]) return false;
+    if (d.lb[x] < d.out_lb[x] + 1 || d.ub[x] > d.out_ub[x] - 1) return false;
+  }
+  return true;
+}
+
+// two_steps: out = apply(apply(in)) in one temporally blocked launch (caller checked tb2_eligible)
 int do_apply(neptune_rt_stencil *s, int n_in, neptune_rt_field *const *in, neptune_rt_field *out, int64_t p0, int64_t p1,
-             cudaStream_t stream) {
+             cudaStream_t stream, bool two_steps = false) {
   neptune_rt_ctx *c = s->ctx;
   const neptune_rt_stencil_desc &d = s->desc.c;
   if (n_in != d.n_inputs) return set_error(c, NEPTUNE_RT_EINVAL, "neptune_rt_apply: %d inputs given, the apply has %d", n_in, d.n_inputs);
@@ -596,7 +623,14 @@ int do_apply(neptune_rt_stencil *s, int n_in, neptune_rt_field *const *in, neptu
   // pick the kernel variant
   const Variant *pick = nullptr;
   const bool tma_ok = tma_eligible(s, n_in, in, out) && encode_tiled() != nullptr;
-  if (s->want == "auto") {
+  if (two_steps) {
+    if (!tma_ok) return set_error(c, NEPTUNE_RT_EINVAL, "temporally blocked launch on fields that are not TMA-eligible");
+    for (auto &v : s->body->variants)
+      if (v.kind == neptune::VARIANT_TB2 && v.fma == s->fma && (s->want_tb == "auto" || v.name == s->want_tb)) { pick = &v; break; }
+    if (!pick)
+      for (auto &v : s->body->variants)
+        if (v.kind == neptune::VARIANT_TB2 && (s->want_tb == "auto" || v.name == s->want_tb)) { pick = &v; break; }
+  } else if (s->want == "auto") {
     if (tma_ok)
       for (auto &v : s->body->variants)
         if (v.kind == neptune::VARIANT_TMA && v.fma == s->fma) { pick = &v; break; }
@@ -613,7 +647,7 @@ int do_apply(neptune_rt_stencil *s, int n_in, neptune_rt_field *const *in, neptu
       return set_error(c, NEPTUNE_RT_EINVAL, "kernel variant '%s' needs inputs that share the result's box and 16-byte aligned rows", pick->name.c_str());
   }
   if (!pick) return set_error(c, NEPTUNE_RT_EUNSUPPORTED, "no kernel variant '%s' for this body", s->want.c_str());
-  if (pick->kind == neptune::VARIANT_TMA) {
+  if (pick->kind != neptune::VARIANT_DIRECT) {
     const CUtensorMap *tm = nullptr;
     if (int rc = get_tmap(s, in[s->body->staged]->dptr, in[s->body->staged]->ext, pick->box_x, pick->box_y, &tm)) return rc;
     a.tmap = tm;
@@ -747,7 +781,14 @@ extern "C" int neptune_rt_run_steps(neptune_rt_stencil *s, neptune_rt_field *fa,
   const int64_t n0 = fa->ext[cd0];
 
   if (c->nranks == 1 || !c->comm) {
-    for (int64_t t = 0; t < nsteps; ++t) {
+    int64_t t = 0;
+    if (s->tblock == 2 && tb2_eligible(s, cur, nxt))
+      for (; t + 2 <= nsteps; t += 2) {  // two steps per launch: reads cur, writes nxt
+        ins[0] = cur;
+        if (int rc = do_apply(s, d.n_inputs, ins, nxt, 0, n0, c->stream, true)) return rc;
+        std::swap(cur, nxt);
+      }
+    for (; t < nsteps; ++t) {
       ins[0] = cur;
       if (int rc = do_apply(s, d.n_inputs, ins, nxt, 0, n0, c->stream)) return rc;
       std::swap(cur, nxt);

@@ -285,3 +285,64 @@ def test_launch_accounting(nb, ctx):
     m.run_steps(ctx, "@entry", [b, a], 7)
     assert ctx.launch_count() - n0 == 7      # one kernel per sweep: no copy-through or store kernels
     m.destroy()
+
+
+@pytest.mark.parametrize("name,shape,ty,steps", [
+    ("heat_star", (40, 48, 64), "f64", 8),
+    ("heat_star", (40, 48, 64), "f64", 7),        # odd: fused pairs + one single sweep
+    ("heat_star", (21, 37, 70), "f64", 6),        # extents that are not multiples of the tile
+    ("heat_star", (150, 20, 136), "f64", 4),      # several z chunks
+    ("heat_star", (24, 40, 72), "f32", 10),
+    ("weighted_3d7", (20, 33, 66), "f64", 6),
+    ("weighted_3d27", (18, 24, 64), "f64", 4),
+])
+def test_temporal_blocking_bit_exact(nb, ctx, name, shape, ty, steps):
+    """tblock=2 (two time steps per launch, sweep_tb2.cuh) == the oracle's step-by-step loop, bitwise,
+    for every compiled temporally blocked kernel; and it really halves the launches."""
+    text, n_extra = H.program(name, list(shape), ty)
+    assert n_extra == 0
+    u, _ = H.inputs(shape, 0, ty, seed=41)
+    want = H.oracle_steps(text, u, [], steps)
+    m = nb.Module(text)
+    try:
+        st = m.stencil(ctx, 0)
+        for tbv in ["tb2:64x16", "tb2:64x16n7", "tb2:128x16", "tb2:64x32"]:
+            st.set("variant", tbv)
+            fa, fb = nb.Field.from_numpy(ctx, u), nb.Field.from_numpy(ctx, u)
+            n0 = ctx.launch_count()
+            r = st.run_steps(fa, fb, [], steps)
+            assert ctx.launch_count() - n0 == steps // 2 + steps % 2
+            got = r.download()
+            assert H.bits_equal(got, want), "%s differs on %s after %d steps" % (tbv, shape, steps)
+            if steps >= 2 and steps % 2 == 0:
+                assert st.variant() == tbv
+            fa.free(); fb.free()
+        st.set("tblock", 1)
+        fa, fb = nb.Field.from_numpy(ctx, u), nb.Field.from_numpy(ctx, u)
+        n0 = ctx.launch_count()
+        r = st.run_steps(fa, fb, [], steps)
+        assert ctx.launch_count() - n0 == steps
+        assert H.bits_equal(r.download(), want)
+        fa.free(); fb.free()
+    finally:
+        m.destroy()
+
+
+def test_temporal_blocking_falls_back_to_single_sweeps(nb, ctx):
+    """Bodies/geometries the fused kernel does not take (extra inputs, 2-D, bounds touching the box)
+    run step by step with the same result — still on the GPU, never on the CPU."""
+    for name, shape in [("jacobi_star", (20, 24, 32)), ("heat_star", (48, 64))]:
+        text, n_extra = H.program(name, list(shape))
+        u, extra = H.inputs(shape, n_extra, "f64", seed=8)
+        want = H.oracle_steps(text, u, extra, 6)
+        m = nb.Module(text)
+        st = m.stencil(ctx, 0).set("tblock", 2)
+        fa, fb = nb.Field.from_numpy(ctx, u), nb.Field.from_numpy(ctx, u)
+        fx = [nb.Field.from_numpy(ctx, e) for e in extra]
+        n0 = ctx.launch_count()
+        r = st.run_steps(fa, fb, fx, 6)
+        assert ctx.launch_count() - n0 == 6
+        assert H.bits_equal(r.download(), want)
+        for f in [fa, fb] + fx:
+            f.free()
+        m.destroy()
