@@ -139,8 +139,9 @@ int neptune_rt_body_compiled(uint64_t key);
 int neptune_rt_stencil_create(neptune_rt_ctx *ctx, const neptune_rt_stencil_desc *desc,
                               neptune_rt_stencil **stencil);
 int neptune_rt_stencil_destroy(neptune_rt_stencil *stencil);
-/* Tuning knobs, all optional: "variant" = "auto" | "direct" | "tma:<cfg>", "zchunk" = planes
- * per work item, "tblock" = fused time steps per launch. Unknown keys return EINVAL. */
+/* Tuning knobs, all optional: "variant" = "auto" | "direct" | "tma:<cfg>" | "tb2:<cfg>", "zchunk" =
+ * planes per work item, "tblock" = time steps fused per launch by neptune_rt_run_steps (0 = auto:
+ * two where the temporally blocked kernel applies, else one; 1; 2). Unknown keys return EINVAL. */
 int neptune_rt_stencil_set(neptune_rt_stencil *stencil, const char *key, const char *value);
 /* The kernel variants compiled for this stencil's body ("direct", "tma:64x16", ...). */
 int neptune_rt_stencil_variant_count(neptune_rt_stencil *stencil);
@@ -157,8 +158,10 @@ int neptune_rt_apply_planes(neptune_rt_stencil *stencil, int n_in, neptune_rt_fi
 /* nsteps sweeps ping-ponging a <-> b (in[0] = a on odd steps' input ...): the host time loop of
  * SURVEY.md §3.3 kept resident on the device. extra[] are inputs 1..n_in-1 (coefficients, rhs).
  * On return *result is a or b, whichever holds the last state. With a communicator attached
- * (neptune_rt_comm_init) every step exchanges `halo` ghost planes with the dim-0 neighbours,
- * overlapped with the interior sweep. */
+ * (neptune_rt_comm_init) every launch exchanges its ghost planes with the dim-0 neighbours,
+ * overlapped with the interior sweep. Where the temporally blocked kernel applies (rank 3, one
+ * input, radius 1, bounds inside the box) two steps are fused per launch; the result is bitwise
+ * the same as nsteps single sweeps. */
 int neptune_rt_run_steps(neptune_rt_stencil *stencil, neptune_rt_field *a, neptune_rt_field *b,
                          int n_extra, neptune_rt_field *const *extra, int64_t nsteps,
                          neptune_rt_field **result);
@@ -173,6 +176,13 @@ int neptune_rt_slab_partition(int64_t n0, int nranks, int rank, int64_t *begin, 
 int neptune_rt_slab_localize(const neptune_rt_stencil_desc *global_desc, int nranks, int rank,
                              int64_t halo, neptune_rt_stencil_desc *local_desc,
                              int64_t *local_in_lb, int64_t *local_in_ub);
+/* Tells a stencil created from a localized descriptor how its box sits in the global domain:
+ * `ghost` planes on every dim-0 side that has a neighbour (the `halo` given to slab_localize) and
+ * the GLOBAL apply bounds along dim 0. With ghost >= 2*radius neptune_rt_run_steps fuses two time
+ * steps per launch and exchanges 2*radius planes every two steps; without this call it assumes
+ * ghost = radius and runs one step per launch. */
+int neptune_rt_stencil_set_slab(neptune_rt_stencil *stencil, int64_t ghost, int64_t global_lb0,
+                                int64_t global_ub0);
 /* 128-byte NCCL unique id (rank 0 creates it; the host harness broadcasts it). */
 int neptune_rt_comm_unique_id(void *id128);
 int neptune_rt_comm_init(neptune_rt_ctx *ctx, const void *id128, int nranks, int rank);

@@ -129,7 +129,11 @@ struct neptune_rt_stencil {
   std::string want = "auto";
   std::string want_tb = "auto";  // which temporally blocked kernel run_steps uses when tblock == 2
   int zchunk = 0;
-  int tblock = 1;
+  int tblock = 0;  // time steps fused per launch: 0 = auto (2 when the launch is eligible), 1, 2
+  // slab mode (neptune_rt_stencil_set_slab): ghost planes per neighbour side of the local box and the
+  // GLOBAL apply bounds along dim 0, which a temporally blocked launch needs for its level-1 planes
+  bool slab_set = false;
+  int64_t slab_ghost = 0, slab_glb0 = 0, slab_gub0 = 0;
   const Variant *last = nullptr;
   std::vector<TmapEntry> tmaps;
 };
@@ -472,7 +476,7 @@ extern "C" int neptune_rt_stencil_set(neptune_rt_stencil *s, const char *key, co
   if (k == "zchunk") { s->zchunk = std::max(0, std::atoi(value)); return NEPTUNE_RT_OK; }
   if (k == "tblock") {
     const int t = std::atoi(value);
-    if (t < 1 || t > 2) return set_error(s->ctx, NEPTUNE_RT_EINVAL, "stencil_set: tblock must be 1 or 2");
+    if (t < 0 || t > 2) return set_error(s->ctx, NEPTUNE_RT_EINVAL, "stencil_set: tblock must be 0 (auto), 1 or 2");
     s->tblock = t;
     return NEPTUNE_RT_OK;
   }
@@ -546,16 +550,26 @@ bool tma_eligible(const neptune_rt_stencil *s, int n_in, neptune_rt_field *const
 // The temporally blocked kernel takes: a body with a tb2 kernel, one input sharing the result's box
 // (TMA-eligible), rank 3, and apply bounds at least one point inside the box on every side (so no
 // in-bounds point of either level reads outside the box; the reference's own fixtures obey this).
-bool tb2_eligible(const neptune_rt_stencil *s, neptune_rt_field *a, neptune_rt_field *b) {
+// In slab mode a dim-0 side that has a neighbour needs two ghost planes instead (level 1 is then
+// evaluated on the first ghost plane from level-0 ghosts, exactly as the neighbour evaluates it).
+bool tb2_eligible(const neptune_rt_stencil *s, neptune_rt_field *a, neptune_rt_field *b, bool slab = false) {
   bool has = false;
   for (auto &v : s->body->variants) has |= v.kind == neptune::VARIANT_TB2;
   const neptune_rt_stencil_desc &d = s->desc.c;
   if (!has || d.rank != 3 || d.n_inputs != 1) return false;
   neptune_rt_field *in1[1] = {a};
   if (!tma_eligible(s, 1, in1, b) || encode_tiled() == nullptr) return false;
-  for (int x = 0; x < 3; ++x) {
+  for (int x = 0; x < 3; ++x)
     if (d.ub[x] <= d.lb[x]) return false;
+  for (int x = slab ? 1 : 0; x < 3; ++x)
     if (d.lb[x] < d.out_lb[x] + 1 || d.ub[x] > d.out_ub[x] - 1) return false;
+  if (slab) {
+    const neptune_rt_ctx *c = s->ctx;
+    if (!s->slab_set) return false;
+    const bool up = c->rank > 0, down = c->rank + 1 < c->nranks;
+    if ((up || down) && s->slab_ghost < 2) return false;
+    if (!up && s->slab_glb0 < d.out_lb[0] + 1) return false;
+    if (!down && s->slab_gub0 > d.out_ub[0] - 1) return false;
   }
   return true;
 }
@@ -613,6 +627,12 @@ int do_apply(neptune_rt_stencil *s, int n_in, neptune_rt_field *const *in, neptu
     a.wlo[x] = 0;
     a.whi[x] = (int)out->ext[x];
   }
+  if (two_steps && s->slab_set && d.rank == 3) {
+    // level-1 planes next to the owned slab lie on ghost planes: test them against the GLOBAL apply
+    // bounds (clipped to the local box), not the owned-plane intersection the local descriptor carries
+    a.blo[0] = (int)(std::max(s->slab_glb0, d.out_lb[0]) - d.out_lb[0]);
+    a.bhi[0] = (int)(std::min(s->slab_gub0, d.out_ub[0]) - d.out_lb[0]);
+  }
   a.wlo[cd0] = (int)p0;
   a.whi[cd0] = (int)p1;
   for (int i = 0; i < s->info.n_consts; ++i) a.consts[i] = s->info.consts[i];
@@ -625,8 +645,15 @@ int do_apply(neptune_rt_stencil *s, int n_in, neptune_rt_field *const *in, neptu
   const bool tma_ok = tma_eligible(s, n_in, in, out) && encode_tiled() != nullptr;
   if (two_steps) {
     if (!tma_ok) return set_error(c, NEPTUNE_RT_EINVAL, "temporally blocked launch on fields that are not TMA-eligible");
-    for (auto &v : s->body->variants)
-      if (v.kind == neptune::VARIANT_TB2 && v.fma == s->fma && (s->want_tb == "auto" || v.name == s->want_tb)) { pick = &v; break; }
+    // auto: the 128x16 tile measured fastest on 512^3 (r01: 408 vs 382 Gupd/s for 64x16); narrow
+    // boxes keep the 64-wide tile so that fewer CTAs idle on a partial column
+    const char *prefer = (s->want_tb == "auto" && out->ext[2] >= 256) ? "tb2:128x16" : nullptr;
+    if (prefer)
+      for (auto &v : s->body->variants)
+        if (v.kind == neptune::VARIANT_TB2 && v.fma == s->fma && v.name == prefer) { pick = &v; break; }
+    if (!pick)
+      for (auto &v : s->body->variants)
+        if (v.kind == neptune::VARIANT_TB2 && v.fma == s->fma && (s->want_tb == "auto" || v.name == s->want_tb)) { pick = &v; break; }
     if (!pick)
       for (auto &v : s->body->variants)
         if (v.kind == neptune::VARIANT_TB2 && (s->want_tb == "auto" || v.name == s->want_tb)) { pick = &v; break; }
@@ -782,7 +809,7 @@ extern "C" int neptune_rt_run_steps(neptune_rt_stencil *s, neptune_rt_field *fa,
 
   if (c->nranks == 1 || !c->comm) {
     int64_t t = 0;
-    if (s->tblock == 2 && tb2_eligible(s, cur, nxt))
+    if (s->tblock != 1 && tb2_eligible(s, cur, nxt))
       for (; t + 2 <= nsteps; t += 2) {  // two steps per launch: reads cur, writes nxt
         ins[0] = cur;
         if (int rc = do_apply(s, d.n_inputs, ins, nxt, 0, n0, c->stream, true)) return rc;
@@ -797,39 +824,57 @@ extern "C" int neptune_rt_run_steps(neptune_rt_stencil *s, neptune_rt_field *fa,
     return NEPTUNE_RT_OK;
   }
 
-  // slab mode: the local box is [own - halo, own + halo) clipped to the global box, as built by
-  // neptune_rt_slab_localize; ghost planes exist on the sides that have a neighbour
-  int64_t halo = 0;
+  // slab mode: the local box is [own - ghost, own + ghost) clipped to the global box, as built by
+  // neptune_rt_slab_localize; ghost planes exist on the sides that have a neighbour.  A launch that
+  // fuses T steps (T = 1, or 2 with temporal blocking) needs T*radius valid ghost planes going in
+  // and refreshes as many coming out: first the T*radius owned planes next to each neighbour, whose
+  // exchange then overlaps the interior launch.
+  int64_t radius = 0;
   for (int i = 0; i < d.n_ops; ++i)
-    if (d.ops[i].opcode == NEPTUNE_RT_OP_ACCESS) halo = std::max<int64_t>(halo, std::llabs(d.ops[i].offset[0]));
+    if (d.ops[i].opcode == NEPTUNE_RT_OP_ACCESS) radius = std::max<int64_t>(radius, std::llabs(d.ops[i].offset[0]));
+  const int64_t ghost = s->slab_set ? s->slab_ghost : radius;
+  if (ghost < radius) return set_error(c, NEPTUNE_RT_EINVAL, "run_steps: %lld ghost planes are fewer than the dim-0 stencil radius", (long long)ghost);
   const bool up = c->rank > 0, down = c->rank + 1 < c->nranks;
-  const int64_t own_b = up ? halo : 0, own_e = n0 - (down ? halo : 0);
-  if (own_e - own_b < 2 * halo) return set_error(c, NEPTUNE_RT_EINVAL, "run_steps: slab of %lld planes is thinner than two halos", (long long)(own_e - own_b));
-  // ghosts of the first input state
+  const int64_t own_b = up ? ghost : 0, own_e = n0 - (down ? ghost : 0);
+  if (own_e - own_b < 2 * ghost) return set_error(c, NEPTUNE_RT_EINVAL, "run_steps: slab of %lld planes is thinner than two halos", (long long)(own_e - own_b));
+  const bool fuse2 = s->tblock != 1 && ghost >= 2 * radius && own_e - own_b >= 4 * radius && tb2_eligible(s, cur, nxt, true);
+  // every ghost plane of the first input state
   RT_CUDA(c, cudaEventRecord(c->ev_boundary, c->stream));
   RT_CUDA(c, cudaStreamWaitEvent(c->halo_stream, c->ev_boundary, 0));
-  if (int rc = neptune_rt_halo_exchange(c, cur, own_b, own_e, halo, c->halo_stream)) return rc;
+  if (int rc = neptune_rt_halo_exchange(c, cur, own_b, own_e, ghost, c->halo_stream)) return rc;
   RT_CUDA(c, cudaEventRecord(c->ev_halo, c->halo_stream));
   RT_CUDA(c, cudaStreamWaitEvent(c->stream, c->ev_halo, 0));
-  for (int64_t t = 0; t < nsteps; ++t) {
+  for (int64_t t = 0; t < nsteps;) {
+    const bool two = fuse2 && t + 2 <= nsteps;
+    const int64_t w = two ? 2 * radius : radius;  // planes computed first and exchanged
     ins[0] = cur;
     // 1. boundary planes of the owned slab, so their exchange can start early
-    if (halo > 0) {
-      if (up) if (int rc = do_apply(s, d.n_inputs, ins, nxt, own_b, own_b + halo, c->stream)) return rc;
-      if (down) if (int rc = do_apply(s, d.n_inputs, ins, nxt, own_e - halo, own_e, c->stream)) return rc;
+    if (w > 0) {
+      if (up) if (int rc = do_apply(s, d.n_inputs, ins, nxt, own_b, own_b + w, c->stream, two)) return rc;
+      if (down) if (int rc = do_apply(s, d.n_inputs, ins, nxt, own_e - w, own_e, c->stream, two)) return rc;
     }
     RT_CUDA(c, cudaEventRecord(c->ev_boundary, c->stream));
     RT_CUDA(c, cudaStreamWaitEvent(c->halo_stream, c->ev_boundary, 0));
     // 2. halo exchange of the new state on the high-priority stream, concurrent with 3.
-    if (int rc = neptune_rt_halo_exchange(c, nxt, own_b, own_e, halo, c->halo_stream)) return rc;
+    if (int rc = neptune_rt_halo_exchange(c, nxt, own_b, own_e, w, c->halo_stream)) return rc;
     RT_CUDA(c, cudaEventRecord(c->ev_halo, c->halo_stream));
     // 3. interior
-    if (int rc = do_apply(s, d.n_inputs, ins, nxt, own_b + (up ? halo : 0), own_e - (down ? halo : 0), c->stream)) return rc;
+    if (int rc = do_apply(s, d.n_inputs, ins, nxt, own_b + (up ? w : 0), own_e - (down ? w : 0), c->stream, two)) return rc;
     // 4. join
     RT_CUDA(c, cudaStreamWaitEvent(c->stream, c->ev_halo, 0));
     std::swap(cur, nxt);
+    t += two ? 2 : 1;
   }
   if (result) *result = cur;
+  return NEPTUNE_RT_OK;
+}
+
+extern "C" int neptune_rt_stencil_set_slab(neptune_rt_stencil *s, int64_t ghost, int64_t global_lb0, int64_t global_ub0) {
+  if (!s || ghost < 0) return set_error(s ? s->ctx : nullptr, NEPTUNE_RT_EINVAL, "stencil_set_slab: bad arguments");
+  s->slab_set = true;
+  s->slab_ghost = ghost;
+  s->slab_glb0 = global_lb0;
+  s->slab_gub0 = global_ub0;
   return NEPTUNE_RT_OK;
 }
 

@@ -99,6 +99,7 @@ def lib() -> C.CDLL:
         "neptune_rt_run_steps": (i32, [vp, vp, vp, i32, C.POINTER(vp), i64, C.POINTER(vp)]),
         "neptune_rt_slab_partition": (i32, [i64, i32, i32, i64p, i64p]),
         "neptune_rt_slab_localize": (i32, [C.POINTER(StencilDescC), i32, i32, i64, C.POINTER(StencilDescC), i64p, i64p]),
+        "neptune_rt_stencil_set_slab": (i32, [vp, i64, i64, i64]),
         "neptune_rt_comm_unique_id": (i32, [vp]),
         "neptune_rt_comm_init": (i32, [vp, vp, i32, i32]),
         "neptune_rt_halo_exchange": (i32, [vp, vp, i64, i64, i64, vp]),
@@ -345,6 +346,12 @@ class Stencil:
 
     def set(self, key: str, value) -> "Stencil":
         self.ctx._check(self.ctx._L.neptune_rt_stencil_set(self.h, key.encode(), str(value).encode()))
+        return self
+
+    def set_slab(self, ghost: int, global_lb0: int, global_ub0: int) -> "Stencil":
+        """Slab mode: ghost planes per neighbour side and the global dim-0 apply bounds (lets
+        run_steps fuse two steps per launch when ghost >= 2 * radius)."""
+        self.ctx._check(self.ctx._L.neptune_rt_stencil_set_slab(self.h, ghost, global_lb0, global_ub0))
         return self
 
     def variant(self) -> str:

@@ -30,6 +30,13 @@ class Slab:
         self.up = rank > 0
         self.down = rank + 1 < nranks
 
+    def stencil(self, ctx: "rt.Context") -> "rt.Stencil":
+        """The local stencil, told where its box sits in the global domain (ghost width and the
+        global dim-0 apply bounds) so that run_steps may fuse two steps per launch."""
+        st = rt.Stencil(ctx, self.local)
+        st.set_slab(self.halo, self.g.lb[0], self.g.ub[0])
+        return st
+
     # rows of the LOCAL storage
     @property
     def own_rows(self) -> Tuple[int, int]:

@@ -20,7 +20,7 @@ def _free_port():
     return p
 
 
-def _worker(rank, world, port, name, shape, steps, q):
+def _worker(rank, world, port, name, shape, steps, q, halo=None, tblock=0):
     import torch
     import torch.distributed as dist
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
@@ -32,12 +32,13 @@ def _worker(rank, world, port, name, shape, steps, q):
         gtext, n_extra = H.program(name, list(shape))
         u, extra = H.inputs(shape, n_extra, "f64", seed=99)
         g = nb.Module(gtext).apply_desc(0)
-        s = Slab(g, world, rank)
+        s = Slab(g, world, rank, halo)
         ctx = nb.Context(rank)
         uid = [nb.comm_unique_id() if rank == 0 else None]
         dist.broadcast_object_list(uid, src=0)
         ctx.comm_init(uid[0], world, rank)
-        st = nb.Stencil(ctx, s.local)
+        st = s.stencil(ctx)
+        st.set("tblock", tblock)
         lb, ub = s.local.out_lb, s.local.out_ub
         fa, fb = nb.Field(ctx, np.float64, lb, ub), nb.Field(ctx, np.float64, lb, ub)
         loc = s.scatter(u)
@@ -50,12 +51,13 @@ def _worker(rank, world, port, name, shape, steps, q):
             fx.append(f)
         res = st.run_steps(fa, fb, fx, steps)
         got = s.owned(res.download()).copy()
+        used = st.variant()
         parts = [None] * world
         dist.all_gather_object(parts, (s.begin, got))
         if rank == 0:
             full = np.concatenate([p[1] for p in sorted(parts, key=lambda p: p[0])], axis=0)
             want = H.oracle_steps(gtext, u, extra, steps)
-            q.put(bool(H.bits_equal(full, want)))
+            q.put((bool(H.bits_equal(full, want)), used))
         for f in [fa, fb] + fx:
             f.free()
         ctx.close()
@@ -63,13 +65,17 @@ def _worker(rank, world, port, name, shape, steps, q):
         dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("name,shape,steps", [
-    ("heat_star", (64, 48, 64), 9),
-    ("heat_box_2d9", (96, 128), 7),
-    ("varcoef_3d7", (32, 16, 32), 4),
-    ("jacobi_star", (40, 32, 64), 6),
+@pytest.mark.parametrize("name,shape,steps,halo,tblock", [
+    ("heat_star", (64, 48, 64), 9, None, 0),
+    ("heat_box_2d9", (96, 128), 7, None, 0),
+    ("varcoef_3d7", (32, 16, 32), 4, None, 0),
+    ("jacobi_star", (40, 32, 64), 6, None, 0),
+    ("heat_star", (64, 48, 64), 9, 2, 0),      # two ghost planes: two steps per launch and per exchange, + one odd step
+    ("heat_star", (96, 40, 136), 8, 2, 2),
+    ("heat_star", (64, 48, 64), 5, 2, 1),      # two ghost planes, temporal blocking switched off
+    ("weighted_3d27", (48, 24, 32), 6, 2, 0),
 ])
-def test_slab_nccl_equals_single_domain(name, shape, steps):
+def test_slab_nccl_equals_single_domain(name, shape, steps, halo, tblock):
     import torch
     import torch.multiprocessing as mp
     ngpu = torch.cuda.device_count()
@@ -79,10 +85,13 @@ def test_slab_nccl_equals_single_domain(name, shape, steps):
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
     port = _free_port()
-    procs = [ctx.Process(target=_worker, args=(r, world, port, name, shape, steps, q)) for r in range(world)]
+    procs = [ctx.Process(target=_worker, args=(r, world, port, name, shape, steps, q, halo, tblock)) for r in range(world)]
     for p in procs:
         p.start()
     for p in procs:
         p.join(300)
         assert p.exitcode == 0
-    assert q.get(timeout=5) is True
+    ok, used = q.get(timeout=5)
+    assert ok is True
+    if halo == 2 and tblock != 1 and name == "heat_star" and steps % 2 == 0:
+        assert used.startswith("tb2:"), used   # the temporally blocked kernel really ran in slab mode
