@@ -40,6 +40,7 @@ WORKLOADS = {
     "c1": ("heat_star", [4096, 4096], "f64", 0.2, 16, "2D 5-pt fp64 heat step, 4096^2 (BASELINE configs[0])"),
     "c5": ("jacobi_star", [768, 768, 768], "f64", None, 24, "3D 7-pt Jacobi with rhs, 768^3 f64 (BASELINE configs[4], 1 GPU)"),
     "c5f32": ("jacobi_star", [768, 768, 768], "f32", None, 12, "3D 7-pt Jacobi with rhs, 768^3 f32 (BASELINE configs[4], 1 GPU)"),
+    "c4": ("varcoef27", [128, 1024, 1024], "f64", None, 232, "3D 27-pt variable-coefficient fp64 (27 coefficient fields), 128x1024x1024 per GPU = 1024^3 over 8 GPUs (BASELINE configs[3])"),
     "tiny": ("heat_star", [64, 64, 128], "f64", 0.1, 16, "3D 7-pt fp64 heat step, 64x64x128 (self-test)"),
 }
 
@@ -53,6 +54,8 @@ def program_text(name, shape):
         return mb.heat_box_2d9(shape, alpha, ty), 0
     if kind == "jacobi_star":
         return mb.jacobi_star(shape, 1.0 / (max(shape) ** 2), ty), 1
+    if kind == "varcoef27":
+        return mb.varcoef(shape, mb.box_offsets(3), ty), 27
     raise KeyError(kind)
 
 
@@ -280,7 +283,11 @@ def run_b200(args):
     extra = []
     for k in range(n_extra):
         f = nb.Field(ctx, dt, lb, ub)
-        f.upload(synth(lshape, ty, 20260500 + k + 100 * rank))
+        c = synth(lshape, ty, 20260500 + k + 100 * rank)
+        if kind == "varcoef27":
+            c = (1.0 + 0.5 * c) / 27.0      # coefficients ~ U(0.4, 1.6)/27: a stable weighted average
+        f.upload(c)
+        ctx.sync()
         extra.append(f)
 
     def barrier():
@@ -367,46 +374,50 @@ def run_b200(args):
         roofline["single_step_kernel"] = single
 
     # ---- e2e: the reference-facing entry call on HOST memrefs, copies inside the timed region -----
-    from neptune_pde_solver_b200 import mlir_builders as mb
-    if world > 1:
-        ltext = {"heat_star": lambda: mb.heat_star(lshape, WORKLOADS[args.workload][3], ty, lb),
-                 "heat_box_2d9": lambda: mb.heat_box_2d9(lshape, WORKLOADS[args.workload][3], ty, lb),
-                 "jacobi_star": lambda: mb.jacobi_star(lshape, 1.0 / (max(gshape) ** 2), ty, lb)}[kind]()
-        emod = nb.Module(ltext)
-    else:
-        emod = mod
-    if args.variant:
-        emod.stencil(ctx, 0).set("variant", args.variant)
-    keep = []
-    hargs = []
-    for k in range(2 + n_extra):
-        t, a = pinned_like(lshape, dt)
-        keep.append(t)
-        hargs.append(a)
-    hargs[1][...] = u
-    for k in range(n_extra):
-        hargs[2 + k][...] = synth(lshape, ty, 20260500 + k + 100 * rank)
-    e_steps = max(1, min(args.steps, args.e2e_steps))
-    for _ in range(2):
-        emod.run(ctx, "@entry", hargs)
-    barrier()
-    l0 = ctx.launch_count()
-    t0 = time.perf_counter()
-    for _ in range(e_steps):
-        emod.run(ctx, "@entry", hargs)          # upload inputs, sweep, download result, sync
-        hargs[0], hargs[1] = hargs[1], hargs[0]  # the host time loop's swap
-    barrier()
-    e_sec = time.perf_counter() - t0
-    e_launches = ctx.launch_count() - l0
-    if world > 1:
-        t = torch.tensor([e_sec], dtype=torch.float64, device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        e_sec = float(t[0])
-    e_value = total_points / (e_sec / e_steps) / 1e9
+    e2e, e_launches = None, 0
     field_bytes = int(np.prod(lshape)) * np.dtype(dt).itemsize
-    e2e = {"value": e_value, "unit": UNIT, "h2d_bytes_per_step": field_bytes * (1 + n_extra) * world,
-           "d2h_bytes_per_step": field_bytes * world, "steps": e_steps, "ms_per_step": e_sec / e_steps * 1e3,
-           "api": "neptune_b200_run_host(@entry(out, in)) on pinned host memrefs, one sweep per call"}
+    if args.e2e_steps > 0:
+        from neptune_pde_solver_b200 import mlir_builders as mb
+        if world > 1:
+            ltext = {"heat_star": lambda: mb.heat_star(lshape, WORKLOADS[args.workload][3], ty, lb),
+                     "heat_box_2d9": lambda: mb.heat_box_2d9(lshape, WORKLOADS[args.workload][3], ty, lb),
+                     "jacobi_star": lambda: mb.jacobi_star(lshape, 1.0 / (max(gshape) ** 2), ty, lb),
+                     "varcoef27": lambda: mb.varcoef(lshape, mb.box_offsets(3), ty, lb)}[kind]()
+            emod = nb.Module(ltext)
+        else:
+            emod = mod
+        if args.variant:
+            emod.stencil(ctx, 0).set("variant", args.variant)
+        keep = []
+        hargs = []
+        for k in range(2 + n_extra):
+            t, a = pinned_like(lshape, dt)
+            keep.append(t)
+            hargs.append(a)
+        hargs[1][...] = u
+        for k in range(n_extra):
+            hargs[2 + k][...] = synth(lshape, ty, 20260500 + k + 100 * rank)
+        e_steps = max(1, min(args.steps, args.e2e_steps))
+        for _ in range(2):
+            emod.run(ctx, "@entry", hargs)
+        barrier()
+        l0 = ctx.launch_count()
+        t0 = time.perf_counter()
+        for _ in range(e_steps):
+            emod.run(ctx, "@entry", hargs)          # upload inputs, sweep, download result, sync
+            hargs[0], hargs[1] = hargs[1], hargs[0]  # the host time loop's swap
+        barrier()
+        e_sec = time.perf_counter() - t0
+        e_launches = ctx.launch_count() - l0
+        if world > 1:
+            t = torch.tensor([e_sec], dtype=torch.float64, device="cuda")
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            e_sec = float(t[0])
+        e_value = total_points / (e_sec / e_steps) / 1e9
+        field_bytes = int(np.prod(lshape)) * np.dtype(dt).itemsize
+        e2e = {"value": e_value, "unit": UNIT, "h2d_bytes_per_step": field_bytes * (1 + n_extra) * world,
+               "d2h_bytes_per_step": field_bytes * world, "steps": e_steps, "ms_per_step": e_sec / e_steps * 1e3,
+               "api": "neptune_b200_run_host(@entry(out, in)) on pinned host memrefs, one sweep per call; upload | sweep | download pipelined over dim-0 plane chunks (neptune_rt_apply_host)"}
 
     # ---- CPU baseline (rank 0, N=1 only): bounded sample of the same workload --------------------
     cpu = None

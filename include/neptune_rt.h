@@ -155,6 +155,15 @@ int neptune_rt_apply(neptune_rt_stencil *stencil, int n_in, neptune_rt_field *co
 /* Sweep only planes [p0, p1) of dim 0 of the result box (slab boundary / interior split). */
 int neptune_rt_apply_planes(neptune_rt_stencil *stencil, int n_in, neptune_rt_field *const *in,
                             neptune_rt_field *out, int64_t p0, int64_t p1, void *stream);
+/* One sweep on HOST buffers, pipelined over dim-0 plane chunks: upload of chunk i+1, sweep of chunk
+ * i and download of chunk i-1 run concurrently (two copy engines + SMs), so the call costs about
+ * max(upload, download) instead of their sum. in_host[k] == NULL means input k is already resident
+ * in in[k]. chunk_planes = 0 picks about 16 chunks. Synchronous: returns when out_host is complete.
+ * Host memory should be pinned. This is what `@entry(out, in)` of the reference's generated code
+ * (one scf.for nest per call on host memrefs) becomes on the B200 path. */
+int neptune_rt_apply_host(neptune_rt_stencil *stencil, int n_in, neptune_rt_field *const *in,
+                          const void *const *in_host, neptune_rt_field *out, void *out_host,
+                          int64_t chunk_planes);
 /* nsteps sweeps ping-ponging a <-> b (in[0] = a on odd steps' input ...): the host time loop of
  * SURVEY.md §3.3 kept resident on the device. extra[] are inputs 1..n_in-1 (coefficients, rhs).
  * On return *result is a or b, whichever holds the last state. With a communicator attached

@@ -37,6 +37,11 @@ struct FnInfo {
   std::vector<bool> arg_written;
   std::map<int, int> fused_store;     // op index of an apply -> op index of the store fused into it
   std::set<int> elided;               // store ops that became no-ops
+  // entry of the form wrap* / load* / ONE apply on argument fields / fused whole store to an argument:
+  // run from host buffers as an upload | sweep | download pipeline (neptune_rt_apply_host)
+  int pipe_apply = -1;                // op index of that apply, -1 when the function has another shape
+  std::vector<int> pipe_in_args;      // argument position of every apply input
+  int pipe_out_arg = -1;
   std::string plan;
 };
 
@@ -203,6 +208,32 @@ void analyze_function(neptune_b200_module &m, const Function &fn, FnInfo &fi) {
         plan << "\n";
         break;
       case HostOp::Constant: break;
+    }
+  }
+  // pipelined host form?
+  {
+    int n_apply = 0, ai = -1;
+    bool simple = true;
+    for (size_t i = 0; i < fn.ops.size(); ++i) {
+      const HostOp &op = fn.ops[i];
+      if (op.kind == HostOp::ApplyOp) { ++n_apply; ai = (int)i; }
+      else if (op.kind == HostOp::ApplyLinear) simple = false;
+      else if (op.kind == HostOp::Store && !fi.elided.count((int)i)) simple = false;
+    }
+    if (simple && n_apply == 1 && fi.fused_store.count(ai)) {
+      const Apply &ap = *fn.ops[ai].apply;
+      std::string droot = root_of(alias, fn.ops[fi.fused_store[ai]].operands[1]);
+      std::vector<int> ins;
+      for (auto &v : ap.inputs) {
+        std::string r = root_of(alias, v);
+        if (argpos.count(r)) ins.push_back(argpos[r]);
+      }
+      if (argpos.count(droot) && ins.size() == ap.inputs.size() && !fi.arg_needs_upload[argpos[droot]]) {
+        fi.pipe_apply = ai;
+        fi.pipe_in_args = ins;
+        fi.pipe_out_arg = argpos[droot];
+        plan << "  host call: upload | sweep | download pipelined over dim-0 plane chunks (neptune_rt_apply_host)\n";
+      }
     }
   }
   for (size_t i = 0; i < fn.args.size(); ++i)
@@ -441,6 +472,18 @@ extern "C" int neptune_b200_run_host(neptune_b200_module *m, neptune_rt_ctx *ctx
   const FnInfo &fi = m->fns.at(fn->name);
   std::vector<neptune_rt_field *> *fields = nullptr;
   if (int rc = bind_args(*m, ctx, *fn, &fields)) return rc;
+  if (fi.pipe_apply >= 0) {
+    Exec ex{*m, ctx, m->per_ctx[ctx], {}};
+    int rc = 0;
+    neptune_rt_stencil *st = ex.stencil(m->apply_index.at(fn->ops[fi.pipe_apply].apply.get()), &rc);
+    if (!st) return rc;
+    std::vector<neptune_rt_field *> ins;
+    std::vector<const void *> hosts;
+    for (int a : fi.pipe_in_args) { ins.push_back((*fields)[a]); hosts.push_back(args[a]); }
+    rc = neptune_rt_apply_host(st, (int)ins.size(), ins.data(), hosts.data(), (*fields)[fi.pipe_out_arg], args[fi.pipe_out_arg], 0);
+    if (rc) m->err = neptune_rt_last_error(ctx);
+    return rc;
+  }
   for (int i = 0; i < n_args; ++i)
     if ((*fields)[i] && fi.arg_needs_upload[i])
       if (int rc = neptune_rt_field_upload((*fields)[i], args[i])) { m->err = neptune_rt_last_error(ctx); return rc; }

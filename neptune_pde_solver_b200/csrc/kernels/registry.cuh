@@ -7,6 +7,7 @@
 #include "sweep_direct.cuh"
 #include "sweep_tma.cuh"
 #include "sweep_tb2.cuh"
+#include "sweep_tb2m.cuh"
 
 namespace neptune {
 
@@ -95,9 +96,11 @@ template <class F, class C, bool FMA> int launch_tma(const SweepArgs &a) {
   return (int)cudaGetLastError();
 }
 
-template <class F, class C, bool FMA> int launch_tb2(const SweepArgs &a) {
-  typedef Tb2Geom<F, C> G;
-  auto kernel = sweep_tb2<F, C, FMA>;
+template <class F, class C, bool FMA, bool MARCH = false> int launch_tb2(const SweepArgs &a) {
+  typedef typename std::conditional<MARCH, Tb2mGeom<F, C>, Tb2Geom<F, C>>::type G;
+  void (*kernel)(const KParams<F>, const CUtensorMap);
+  if constexpr (MARCH) kernel = sweep_tb2m<F, C, FMA>;
+  else kernel = sweep_tb2<F, C, FMA>;
   static int occ_cached[16] = {0};
   int dev = 0;
   cudaGetDevice(&dev);
@@ -132,8 +135,8 @@ template <class F, class C, bool FMA> int launch_tb2(const SweepArgs &a) {
   return (int)cudaGetLastError();
 }
 
-template <class F, class C, bool FMA> Variant tb2_variant(const char *name) {
-  typedef Tb2Geom<F, C> G;
+template <class F, class C, bool FMA, bool MARCH = false> Variant tb2_variant(const char *name) {
+  typedef typename std::conditional<MARCH, Tb2mGeom<F, C>, Tb2Geom<F, C>>::type G;
   Variant v;
   v.name = name;
   v.kind = VARIANT_TB2;
@@ -143,7 +146,7 @@ template <class F, class C, bool FMA> Variant tb2_variant(const char *name) {
   v.box_x = G::P0; v.box_y = G::BOX_Y;
   v.halo_x = 2 * G::VX; v.halo_y = 2;
   v.threads = G::THREADS; v.smem = G::SMEM_BYTES;
-  v.launch = &launch_tb2<F, C, FMA>;
+  v.launch = &launch_tb2<F, C, FMA, MARCH>;
   return v;
 }
 
@@ -169,6 +172,11 @@ typedef Tb2Cfg<64, 16, 2, 5, 2> Tb2A;       // two time steps per launch (sweep_
 typedef Tb2Cfg<64, 16, 2, 7, 1> Tb2B;
 typedef Tb2Cfg<128, 16, 2, 5, 1> Tb2C;
 typedef Tb2Cfg<64, 32, 4, 5, 1> Tb2D;
+// z-marching form (sweep_tb2m.cuh).  Registers are granted per warp in units of 512, so a CTA of 704
+// threads (128x16 tile) gets 80 per thread and spills; 128x14 is 640 threads -> 96 registers.
+typedef Tb2Cfg<128, 14, 2, 6, 1> Tb2mA;
+typedef Tb2Cfg<64, 16, 2, 6, 2> Tb2mB;
+typedef Tb2Cfg<128, 14, 2, 8, 1> Tb2mC;
 typedef TileCfg<64, 8, 1, 6, 1> Tile3W;   // many-input bodies (one coefficient field per tap)
 typedef TileCfg<128, 32, 8, 3, 2> Tile2A;
 typedef TileCfg<128, 16, 4, 4, 2> Tile2B;
@@ -202,6 +210,12 @@ template <class F> struct BodyRegistrar {
           e.variants.push_back(tb2_variant<F, Tb2B, false>("tb2:64x16n7"));
           e.variants.push_back(tb2_variant<F, Tb2C, false>("tb2:128x16"));
           e.variants.push_back(tb2_variant<F, Tb2D, false>("tb2:64x32"));
+          if constexpr (F::ZSTAR) {
+            e.variants.push_back(tb2_variant<F, Tb2mA, false, true>("tb2m:128x14"));
+            e.variants.push_back(tb2_variant<F, Tb2mA, true, true>("tb2m:128x14"));
+            e.variants.push_back(tb2_variant<F, Tb2mB, false, true>("tb2m:64x16"));
+            e.variants.push_back(tb2_variant<F, Tb2mC, false, true>("tb2m:128x14n8"));
+          }
         }
       } else {
         e.variants.push_back(tma_variant<F, Tile2A, false>("tma:128x32"));

@@ -96,6 +96,8 @@ struct neptune_rt_ctx {
   cudaStream_t halo_stream = nullptr;  // halo exchange, high priority
   cudaEvent_t ev_boundary = nullptr, ev_halo = nullptr;
   cudaEvent_t ev_t0 = nullptr, ev_t1 = nullptr;
+  cudaStream_t h2d_stream = nullptr, d2h_stream = nullptr;  // copy engines of the pipelined host path
+  std::vector<cudaEvent_t> ev_pool;                          // per-chunk events of neptune_rt_apply_host
   int64_t launches = 0;
   std::string err;
   ncclComm_t comm = nullptr;
@@ -244,6 +246,8 @@ extern "C" int neptune_rt_init(int device, neptune_rt_ctx **out) {
   RT_CUDA(nullptr, cudaEventCreateWithFlags(&c->ev_halo, cudaEventDisableTiming));
   RT_CUDA(nullptr, cudaEventCreate(&c->ev_t0));
   RT_CUDA(nullptr, cudaEventCreate(&c->ev_t1));
+  RT_CUDA(nullptr, cudaStreamCreateWithFlags(&c->h2d_stream, cudaStreamNonBlocking));
+  RT_CUDA(nullptr, cudaStreamCreateWithFlags(&c->d2h_stream, cudaStreamNonBlocking));
   *out = c;
   return NEPTUNE_RT_OK;
 }
@@ -276,6 +280,11 @@ extern "C" int neptune_rt_finalize(neptune_rt_ctx *c) {
   cudaEventDestroy(c->ev_t1);
   cudaStreamDestroy(c->stream);
   cudaStreamDestroy(c->halo_stream);
+  cudaStreamSynchronize(c->h2d_stream);
+  cudaStreamSynchronize(c->d2h_stream);
+  cudaStreamDestroy(c->h2d_stream);
+  cudaStreamDestroy(c->d2h_stream);
+  for (cudaEvent_t e : c->ev_pool) cudaEventDestroy(e);
   delete c;
   return NEPTUNE_RT_OK;
 }
@@ -283,7 +292,9 @@ extern "C" int neptune_rt_finalize(neptune_rt_ctx *c) {
 extern "C" int neptune_rt_sync(neptune_rt_ctx *c) {
   if (!c) return set_error(nullptr, NEPTUNE_RT_EINVAL, "neptune_rt_sync: NULL ctx");
   RT_CUDA(c, cudaStreamSynchronize(c->halo_stream));
+  RT_CUDA(c, cudaStreamSynchronize(c->h2d_stream));
   RT_CUDA(c, cudaStreamSynchronize(c->stream));
+  RT_CUDA(c, cudaStreamSynchronize(c->d2h_stream));
   return NEPTUNE_RT_OK;
 }
 
@@ -456,7 +467,7 @@ extern "C" int neptune_rt_stencil_destroy(neptune_rt_stencil *s) {
 extern "C" int neptune_rt_stencil_set(neptune_rt_stencil *s, const char *key, const char *value) {
   if (!s || !key || !value) return set_error(s ? s->ctx : nullptr, NEPTUNE_RT_EINVAL, "stencil_set: NULL argument");
   const std::string k = key, v = value;
-  if (k == "variant" && v.rfind("tb2:", 0) == 0) {
+  if (k == "variant" && v.rfind("tb2", 0) == 0) {
     bool found = false;
     for (auto &var : s->body->variants) found |= var.name == v && var.kind == neptune::VARIANT_TB2;
     if (!found) return set_error(s->ctx, NEPTUNE_RT_EINVAL, "stencil_set: this body has no temporally blocked kernel '%s'", value);
@@ -645,12 +656,17 @@ int do_apply(neptune_rt_stencil *s, int n_in, neptune_rt_field *const *in, neptu
   const bool tma_ok = tma_eligible(s, n_in, in, out) && encode_tiled() != nullptr;
   if (two_steps) {
     if (!tma_ok) return set_error(c, NEPTUNE_RT_EINVAL, "temporally blocked launch on fields that are not TMA-eligible");
-    // auto: the 128x16 tile measured fastest on 512^3 (r01: 408 vs 382 Gupd/s for 64x16); narrow
-    // boxes keep the 64-wide tile so that fewer CTAs idle on a partial column
-    const char *prefer = (s->want_tb == "auto" && out->ext[2] >= 256) ? "tb2:128x16" : nullptr;
-    if (prefer)
-      for (auto &v : s->body->variants)
-        if (v.kind == neptune::VARIANT_TB2 && v.fma == s->fma && v.name == prefer) { pick = &v; break; }
+    // auto: on wide boxes the z-marching form where the body has one (r01, 512^3: tb2m:128x14 427,
+    // tb2:128x16 409, tb2:64x16 382 Gupd/s); narrow boxes keep the 64-wide tile so that fewer CTAs idle on a partial column
+    if (s->want_tb == "auto") {
+      const bool wide = out->ext[2] >= 256;
+      const char *prefer[] = {wide ? "tb2m:128x14" : "tb2:64x16", wide ? "tb2:128x16" : "tb2:64x16"};
+      for (const char *name : prefer) {
+        for (auto &v : s->body->variants)
+          if (v.kind == neptune::VARIANT_TB2 && v.fma == s->fma && v.name == name) { pick = &v; break; }
+        if (pick) break;
+      }
+    }
     if (!pick)
       for (auto &v : s->body->variants)
         if (v.kind == neptune::VARIANT_TB2 && v.fma == s->fma && (s->want_tb == "auto" || v.name == s->want_tb)) { pick = &v; break; }
@@ -698,6 +714,80 @@ extern "C" int neptune_rt_apply_planes(neptune_rt_stencil *s, int n_in, neptune_
                                        int64_t p0, int64_t p1, void *stream) {
   if (!s || !out) return set_error(s ? s->ctx : nullptr, NEPTUNE_RT_EINVAL, "neptune_rt_apply_planes: NULL argument");
   return do_apply(s, n_in, in, out, p0, p1, stream ? (cudaStream_t)stream : s->ctx->stream);
+}
+
+// One sweep on HOST buffers as a three-stage pipeline over dim-0 plane chunks: chunk i+1 uploads
+// (copy engine, H2D) while chunk i is swept (SMs) and chunk i-1 downloads (copy engine, D2H), so a
+// call costs max(upload, download) + one chunk instead of upload + sweep + download.  A chunk of
+// output planes [a, b) reads input planes [a - r, b + r): its launch waits for the upload of the
+// next chunk too.  The sweep of a chunk writes whole planes (copy-through outside `bounds`), so the
+// downloaded result is the full result box (DataflowLowering.cpp:282-287 + :289-444).
+extern "C" int neptune_rt_apply_host(neptune_rt_stencil *s, int n_in, neptune_rt_field *const *in, const void *const *in_host,
+                                     neptune_rt_field *out, void *out_host, int64_t chunk_planes) {
+  if (!s || !in || !in_host || !out || !out_host) return set_error(s ? s->ctx : nullptr, NEPTUNE_RT_EINVAL, "neptune_rt_apply_host: NULL argument");
+  neptune_rt_ctx *c = s->ctx;
+  const neptune_rt_stencil_desc &d = s->desc.c;
+  if (n_in != d.n_inputs) return set_error(c, NEPTUNE_RT_EINVAL, "neptune_rt_apply_host: %d inputs given, the apply has %d", n_in, d.n_inputs);
+  const int cd0 = 3 - d.rank;
+  const int64_t n0 = out->ext[cd0];
+  int64_t radius = 0;
+  for (int i = 0; i < d.n_ops; ++i)
+    if (d.ops[i].opcode == NEPTUNE_RT_OP_ACCESS) radius = std::max<int64_t>(radius, std::llabs(d.ops[i].offset[0]));
+  bool same_rows = true;
+  for (int k = 0; k < n_in; ++k)
+    same_rows &= in[k] && in[k]->rank == out->rank && in[k]->lb[0] == out->lb[0] && in[k]->ub[0] == out->ub[0];
+  if (chunk_planes <= 0) {
+    // about 16 chunks, at least 8 MiB each so that a copy runs at full PCIe rate
+    const size_t plane = n0 ? out->bytes / (size_t)n0 : 1;
+    chunk_planes = std::max<int64_t>((n0 + 15) / 16, (int64_t)(((size_t)8 << 20) + plane - 1) / (int64_t)std::max<size_t>(plane, 1));
+  }
+  chunk_planes = std::max<int64_t>(chunk_planes, std::max<int64_t>(radius, 1));
+  const int64_t nchunks = n0 > 0 ? (n0 + chunk_planes - 1) / chunk_planes : 0;
+  if (!same_rows || nchunks < 3) {
+    // not worth a pipeline (or inputs on another dim-0 box): upload, sweep, download in order
+    for (int k = 0; k < n_in; ++k)
+      if (in_host[k]) if (int rc = neptune_rt_field_upload(in[k], in_host[k])) return rc;
+    if (int rc = neptune_rt_apply(s, n_in, in, out)) return rc;
+    if (int rc = neptune_rt_field_download(out, out_host)) return rc;
+    return neptune_rt_sync(c);
+  }
+  cudaSetDevice(c->device);
+  while ((int64_t)c->ev_pool.size() < 2 * nchunks) {
+    cudaEvent_t e;
+    RT_CUDA(c, cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    c->ev_pool.push_back(e);
+  }
+  // everything queued earlier on the sweep stream (previous call's work on these fields) goes first
+  RT_CUDA(c, cudaEventRecord(c->ev_boundary, c->stream));
+  RT_CUDA(c, cudaStreamWaitEvent(c->h2d_stream, c->ev_boundary, 0));
+  RT_CUDA(c, cudaStreamWaitEvent(c->d2h_stream, c->ev_boundary, 0));
+  auto rows = [&](int64_t i, int64_t *a, int64_t *b) { *a = i * chunk_planes; *b = std::min(n0, *a + chunk_planes); };
+  auto sweep = [&](int64_t i) -> int {
+    int64_t a, b;
+    rows(i, &a, &b);
+    RT_CUDA(c, cudaStreamWaitEvent(c->stream, c->ev_pool[(size_t)std::min(i + 1, nchunks - 1)], 0));
+    if (int rc = do_apply(s, n_in, in, out, a, b, c->stream)) return rc;
+    RT_CUDA(c, cudaEventRecord(c->ev_pool[(size_t)(nchunks + i)], c->stream));
+    RT_CUDA(c, cudaStreamWaitEvent(c->d2h_stream, c->ev_pool[(size_t)(nchunks + i)], 0));
+    size_t off, len;
+    if (int rc = plane_range(out, a, b, &off, &len)) return rc;
+    RT_CUDA(c, cudaMemcpyAsync((char *)out_host + off, (const char *)out->dptr + off, len, cudaMemcpyDeviceToHost, c->d2h_stream));
+    return NEPTUNE_RT_OK;
+  };
+  for (int64_t i = 0; i < nchunks; ++i) {
+    int64_t a, b;
+    rows(i, &a, &b);
+    for (int k = 0; k < n_in; ++k) {
+      if (!in_host[k]) continue;
+      size_t off, len;
+      if (int rc = plane_range(in[k], a, b, &off, &len)) return rc;
+      RT_CUDA(c, cudaMemcpyAsync((char *)in[k]->dptr + off, (const char *)in_host[k] + off, len, cudaMemcpyHostToDevice, c->h2d_stream));
+    }
+    RT_CUDA(c, cudaEventRecord(c->ev_pool[(size_t)i], c->h2d_stream));
+    if (i >= 1) if (int rc = sweep(i - 1)) return rc;
+  }
+  if (int rc = sweep(nchunks - 1)) return rc;
+  return neptune_rt_sync(c);
 }
 
 // ---------------------------------------------------------------------------------------------

@@ -96,6 +96,7 @@ def lib() -> C.CDLL:
         "neptune_rt_stencil_variant_name": (C.c_char_p, [vp, i32]),
         "neptune_rt_apply": (i32, [vp, i32, C.POINTER(vp), vp]),
         "neptune_rt_apply_planes": (i32, [vp, i32, C.POINTER(vp), vp, i64, i64, vp]),
+        "neptune_rt_apply_host": (i32, [vp, i32, C.POINTER(vp), C.POINTER(vp), vp, vp, i64]),
         "neptune_rt_run_steps": (i32, [vp, vp, vp, i32, C.POINTER(vp), i64, C.POINTER(vp)]),
         "neptune_rt_slab_partition": (i32, [i64, i32, i32, i64p, i64p]),
         "neptune_rt_slab_localize": (i32, [C.POINTER(StencilDescC), i32, i32, i64, C.POINTER(StencilDescC), i64p, i64p]),
@@ -368,6 +369,16 @@ class Stencil:
         else:
             rc = self.ctx._L.neptune_rt_apply_planes(self.h, len(ins), arr, out.h, planes[0], planes[1], stream or None)
         self.ctx._check(rc)
+
+    def apply_host(self, ins: Sequence[Field], ins_host: Sequence[Optional[np.ndarray]], out: Field,
+                   out_host: np.ndarray, chunk_planes: int = 0):
+        """One sweep on host arrays, upload | sweep | download pipelined over dim-0 plane chunks
+        (neptune_rt_apply_host). ins_host[k] None = input k is already resident in ins[k]."""
+        arr = (C.c_void_p * len(ins))(*[f.h for f in ins])
+        keep = [None if h is None else np.ascontiguousarray(h) for h in ins_host]
+        hp = (C.c_void_p * len(ins))(*[None if h is None else h.ctypes.data for h in keep])
+        assert out_host.flags["C_CONTIGUOUS"]
+        self.ctx._check(self.ctx._L.neptune_rt_apply_host(self.h, len(ins), arr, hp, out.h, out_host.ctypes.data, chunk_planes))
 
     def run_steps(self, a: Field, b: Field, extra: Sequence[Field], nsteps: int) -> Field:
         arr = (C.c_void_p * max(1, len(extra)))(*[f.h for f in extra])
