@@ -360,8 +360,14 @@ def run_b200(args):
     peak = float(peaks.get("hbm_gbs", 6650.0))
     peak_kind = "measured (MEASURED_PEAKS.json hbm_gbs)" if "hbm_gbs" in peaks else "fallback 6650 GB/s (B200_PROFILING.md)"
     achieved = box_points * bytes_per_update * steps_per_launch / (kernel_ms * 1e-3) / 1e9
+    traffic = args.traffic
+    if traffic is None and world == 1:
+        try:   # per-launch DRAM bytes of this kernel from the committed ncu --set full capture
+            traffic = json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get(args.workload, {}).get(variant)
+        except (OSError, ValueError):
+            traffic = None
     roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                "traffic": args.traffic, "peak_kind": peak_kind, "frac_of_8TBps": achieved / 8000.0,
+                "traffic": traffic, "peak_kind": peak_kind, "frac_of_8TBps": achieved / 8000.0,
                 "kernel": "sweep_%s<%s>" % (variant.split(":")[0], kind), "kernel_ms": kernel_ms,
                 "algorithmic_bytes_per_launch": box_points * bytes_per_update * steps_per_launch,
                 "steps_per_launch": steps_per_launch,
