@@ -62,6 +62,10 @@ const char *neptune_b200_apply_cuda_source(neptune_b200_module *module, int inde
  * Uploads, runs every apply on the GPU, downloads what was written. */
 int neptune_b200_run_host(neptune_b200_module *module, neptune_rt_ctx *ctx, const char *function,
                           int n_args, void *const *args);
+/* Scalar values (results of `neptune_ir.reduce`, NeptuneIROps.td:272-299) the function returned in
+ * the last neptune_b200_run_host, in return-operand order. Writes at most `capacity` of them to
+ * `out` and returns how many there are. */
+int neptune_b200_last_scalars(neptune_b200_module *module, double *out, int capacity);
 /* The host time loop "call entry(out, in, extra...) then swap out/in", nsteps times, kept
  * resident on the device: one upload, nsteps sweeps, one download. On return args[1] holds the
  * final state if nsteps is even, args[0] if odd (exactly what the swapped host loop leaves), and

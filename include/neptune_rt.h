@@ -130,6 +130,16 @@ int64_t neptune_rt_field_bytes(neptune_rt_field *field);
 int neptune_rt_field_store(neptune_rt_field *dst, neptune_rt_field *src, const int64_t *lb,
                            const int64_t *ub);
 
+/* `neptune_ir.reduce` kind = "sum" (NeptuneIROps.td:272-299, ReduceLowering in
+ * lib/Passes/DataflowLowering.cpp:589-698): the sum of the field over [lb, ub) (logical coordinates;
+ * NULL = the whole box). The reference adds element by element in row-major order; this is a
+ * deterministic fixed-partition parallel sum accumulated in fp64 (rounded to f32 for f32 fields), so
+ * parity is the tolerance tier: |gpu - ref| <= n * eps(elem) * sum|x|. With allreduce != 0 and a
+ * communicator attached, the per-rank sums are added across ranks (ncclAllReduce): pass bounds clipped
+ * to the rank's owned planes. Synchronous. */
+int neptune_rt_field_reduce_sum(neptune_rt_field *field, const int64_t *lb, const int64_t *ub,
+                                int allreduce, double *result);
+
 /* ---- stencils -------------------------------------------------------------------------- */
 /* 64-bit structure key of a body (constants' values, bounds and extents excluded): two applies
  * with the same key run the same compiled kernel. Pure host code. */

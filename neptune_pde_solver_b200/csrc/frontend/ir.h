@@ -63,13 +63,13 @@ struct Apply {
 };
 
 struct HostOp {
-  enum Kind { Wrap, Unwrap, Load, Store, ApplyOp, ApplyLinear, Return, Constant } kind;
+  enum Kind { Wrap, Unwrap, Load, Store, ApplyOp, ApplyLinear, Return, Constant, Reduce } kind;
   std::vector<std::string> results, operands;
   std::vector<Type> types;
   std::shared_ptr<Apply> apply;
   std::string callee;
   bool has_bounds = false;
-  Bounds bounds;  // store
+  Bounds bounds;  // store, reduce (callee holds the reduce kind)
   int line = 0;
 };
 

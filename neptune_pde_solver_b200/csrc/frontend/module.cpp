@@ -61,6 +61,7 @@ struct neptune_b200_module {
     std::map<int, int> cursor;                                          // temps of that apply taken in this run
   };
   std::map<neptune_rt_ctx *, PerCtx> per_ctx;
+  std::vector<double> last_scalars;   // scalar results returned by the last run_host
   std::string err;
 };
 
@@ -202,6 +203,17 @@ void analyze_function(neptune_b200_module &m, const Function &fn, FnInfo &fi) {
              << (op.has_bounds ? bounds_str(op.bounds) : std::string("whole")) << ")\n";
         break;
       }
+      case HostOp::Reduce: {
+        if (op.types[0].kind != Type::Grid) throw Diagnostic("line " + std::to_string(op.line) + ": reduce input must be a !neptune_ir.temp");
+        if (op.types[1].kind != Type::Float) throw Diagnostic("line " + std::to_string(op.line) + ": reduce of a non-float element type is not on the B200 path", true);
+        std::string r = root_of(alias, op.operands[0]);
+        if (argpos.count(r) && !touched.count(r)) fi.arg_needs_upload[argpos[r]] = true;
+        touched.insert(r);
+        vtype[op.results[0]] = op.types[1];
+        plan << "  " << op.results[0] << " = reduce " << op.operands[0] << "  -> neptune_rt_field_reduce_sum("
+             << (op.has_bounds ? bounds_str(op.bounds) : std::string("whole")) << ")\n";
+        break;
+      }
       case HostOp::Return:
         plan << "  return";
         for (auto &v : op.operands) plan << " " << v;
@@ -217,7 +229,7 @@ void analyze_function(neptune_b200_module &m, const Function &fn, FnInfo &fi) {
     for (size_t i = 0; i < fn.ops.size(); ++i) {
       const HostOp &op = fn.ops[i];
       if (op.kind == HostOp::ApplyOp) { ++n_apply; ai = (int)i; }
-      else if (op.kind == HostOp::ApplyLinear) simple = false;
+      else if (op.kind == HostOp::ApplyLinear || op.kind == HostOp::Reduce) simple = false;
       else if (op.kind == HostOp::Store && !fi.elided.count((int)i)) simple = false;
     }
     if (simple && n_apply == 1 && fi.fused_store.count(ai)) {
@@ -248,6 +260,8 @@ struct Exec {
   neptune_rt_ctx *ctx;
   neptune_b200_module::PerCtx &pc;
   std::vector<neptune_rt_field *> scratch;  // temps of opdef calls, freed by the caller of run()
+  std::map<std::string, double> scalars;    // results of reduce ops
+  std::vector<double> returned;             // scalar values the top-level function returned
 
   int fail(int code, const std::string &msg) {
     m.err = msg;
@@ -331,8 +345,21 @@ struct Exec {
           if (rc) return rt_fail(rc);
           break;
         }
+        case HostOp::Reduce: {
+          neptune_rt_field *src = env[op.operands[0]];
+          if (!src) return fail(NEPTUNE_RT_EINVAL, "reduce operand has no storage");
+          double v = 0;
+          if (int rc = neptune_rt_field_reduce_sum(src, op.has_bounds ? op.bounds.lb.data() : nullptr,
+                                                   op.has_bounds ? op.bounds.ub.data() : nullptr, 0, &v))
+            return rt_fail(rc);
+          scalars[op.results[0]] = v;
+          break;
+        }
         case HostOp::Return:
-          if (ret) *ret = op.operands.empty() ? nullptr : env[op.operands[0]];
+          returned.clear();
+          for (auto &v : op.operands)
+            if (scalars.count(v)) returned.push_back(scalars[v]);
+          if (ret) *ret = (op.operands.empty() || scalars.count(op.operands[0])) ? nullptr : env[op.operands[0]];
           return NEPTUNE_RT_OK;
         case HostOp::Constant: break;
       }
@@ -490,11 +517,19 @@ extern "C" int neptune_b200_run_host(neptune_b200_module *m, neptune_rt_ctx *ctx
   Exec ex{*m, ctx, m->per_ctx[ctx], {}};
   ex.pc.cursor.clear();
   if (int rc = ex.run(*fn, *fields, nullptr)) return rc;
+  m->last_scalars = ex.returned;
   for (int i = 0; i < n_args; ++i)
     if ((*fields)[i] && fi.arg_written[i])
       if (int rc = neptune_rt_field_download((*fields)[i], args[i])) { m->err = neptune_rt_last_error(ctx); return rc; }
   if (int rc = neptune_rt_sync(ctx)) { m->err = neptune_rt_last_error(ctx); return rc; }
   return NEPTUNE_RT_OK;
+}
+
+extern "C" int neptune_b200_last_scalars(neptune_b200_module *m, double *out, int capacity) {
+  if (!m) return 0;
+  const int n = (int)m->last_scalars.size();
+  for (int i = 0; i < n && i < capacity && out; ++i) out[i] = m->last_scalars[i];
+  return n;
 }
 
 extern "C" int neptune_b200_run_steps_host(neptune_b200_module *m, neptune_rt_ctx *ctx, const char *function, int n_args,

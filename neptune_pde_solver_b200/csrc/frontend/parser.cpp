@@ -479,6 +479,31 @@ class Parser {
       }
       return op;
     }
+    if (n == "neptune_ir.reduce") {  // $input (`in` $bounds)? attr-dict : type -> type  (NeptuneIROps.td:272-299)
+      op.kind = HostOp::Reduce;
+      if (op.results.size() != 1) fail("neptune_ir.reduce must have exactly one result");
+      op.operands.push_back(expect_id('%'));
+      if (lx_.peek().kind == Tok::Word && lx_.peek().text == "in") {
+        lx_.next();
+        op.bounds = parse_bounds();
+        op.has_bounds = true;
+      }
+      if (accept("{")) {
+        expect_word("kind"); expect("=");
+        Tok k = lx_.next();
+        if (k.kind != Tok::Str) fail("reduce kind must be a string");
+        op.callee = k.text;
+        expect("}");
+      }
+      expect(":");
+      op.types.push_back(parse_type());
+      expect("->");
+      op.types.push_back(parse_type());
+      if (op.callee != "sum")
+        throw Diagnostic("line " + std::to_string(name.line) + ": neptune_ir.reduce kind \"" + op.callee +
+                             "\" is not lowered (the reference lowers only \"sum\", DataflowLowering.cpp:655-657)", true);
+      return op;
+    }
     if (n == "neptune_ir.apply") {
       op.kind = HostOp::ApplyOp;
       if (op.results.size() != 1) fail("neptune_ir.apply must have exactly one result");

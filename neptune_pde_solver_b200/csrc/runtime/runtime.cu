@@ -42,6 +42,7 @@ struct NcclApi {
   ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
   ncclResult_t (*Send)(const void *, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
   ncclResult_t (*Recv)(void *, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
+  ncclResult_t (*AllReduce)(const void *, void *, size_t, ncclDataType_t, ncclRedOp_t, ncclComm_t, cudaStream_t) = nullptr;
   ncclResult_t (*GroupStart)() = nullptr;
   ncclResult_t (*GroupEnd)() = nullptr;
   const char *(*GetErrorString)(ncclResult_t) = nullptr;
@@ -74,11 +75,12 @@ NcclApi &nccl() {
   NB_SYM(CommDestroy, "ncclCommDestroy");
   NB_SYM(Send, "ncclSend");
   NB_SYM(Recv, "ncclRecv");
+  NB_SYM(AllReduce, "ncclAllReduce");
   NB_SYM(GroupStart, "ncclGroupStart");
   NB_SYM(GroupEnd, "ncclGroupEnd");
   NB_SYM(GetErrorString, "ncclGetErrorString");
 #undef NB_SYM
-  api.ok = api.GetUniqueId && api.CommInitRank && api.CommDestroy && api.Send && api.Recv && api.GroupStart &&
+  api.ok = api.GetUniqueId && api.CommInitRank && api.CommDestroy && api.Send && api.Recv && api.AllReduce && api.GroupStart &&
            api.GroupEnd && api.GetErrorString;
   return api;
 }
@@ -96,6 +98,8 @@ struct neptune_rt_ctx {
   cudaStream_t halo_stream = nullptr;  // halo exchange, high priority
   cudaEvent_t ev_boundary = nullptr, ev_halo = nullptr;
   cudaEvent_t ev_t0 = nullptr, ev_t1 = nullptr;
+  double *red_partials = nullptr;   // REDUCE_BLOCKS + 1 doubles of device scratch (neptune_rt_field_reduce_sum)
+  double *red_host = nullptr;       // pinned result word
   cudaStream_t h2d_stream = nullptr, d2h_stream = nullptr;  // copy engines of the pipelined host path
   std::vector<cudaEvent_t> ev_pool;                          // per-chunk events of neptune_rt_apply_host
   int64_t launches = 0;
@@ -185,6 +189,52 @@ __global__ void box_copy_kernel(T *dst, const T *src, long long d_sz, long long 
   if (x >= bx || y >= by) return;
   for (int z = blockIdx.z; z < bz; z += gridDim.z)
     dst[(long long)z * d_sz + (long long)y * d_sy + x] = src[(long long)z * s_sz + (long long)y * s_sy + x];
+}
+
+// `neptune_ir.reduce` kind = "sum" (DataflowLowering.cpp:589-698) over a sub-box.  The reference adds the
+// elements one by one in row-major order; a parallel sum cannot keep that association, so this is the
+// tolerance tier: fp64 accumulation for both element types, a FIXED partition (row r of the box goes
+// to block r mod REDUCE_BLOCKS, element x of a row to thread x mod 256) and fixed-shape trees, so the
+// result is deterministic run to run and independent of the GPU's scheduling.
+constexpr int REDUCE_BLOCKS = 592;   // 4 per SM on a 148-SM B200
+constexpr int REDUCE_THREADS = 256;
+
+__device__ __forceinline__ double block_sum_256(double v, double *sh) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_down_sync(0xffffffffu, v, o);
+  if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = v;
+  __syncthreads();
+  double t = 0.0;
+  if (threadIdx.x < 32) {
+    t = threadIdx.x < REDUCE_THREADS / 32 ? sh[threadIdx.x] : 0.0;
+#pragma unroll
+    for (int o = 4; o > 0; o >>= 1) t += __shfl_down_sync(0xffffffffu, t, o);
+  }
+  __syncthreads();
+  return t;  // valid in thread 0
+}
+
+template <class T>
+__global__ void __launch_bounds__(REDUCE_THREADS) reduce_sum_rows(const T *__restrict__ src, long long sz, long long sy,
+                                                                  int bz, int by, int bx, double *__restrict__ partials) {
+  __shared__ double sh[REDUCE_THREADS / 32];
+  double acc = 0.0;
+  const long long rows = (long long)bz * by;
+  for (long long r = blockIdx.x; r < rows; r += gridDim.x) {
+    const long long z = r / by, y = r - z * by;
+    const T *row = src + z * sz + y * sy;
+    for (int x = threadIdx.x; x < bx; x += REDUCE_THREADS) acc += (double)__ldg(row + x);
+  }
+  const double t = block_sum_256(acc, sh);
+  if (threadIdx.x == 0) partials[blockIdx.x] = t;
+}
+
+__global__ void __launch_bounds__(REDUCE_THREADS) reduce_sum_final(const double *__restrict__ partials, int n, double *__restrict__ out) {
+  __shared__ double sh[REDUCE_THREADS / 32];
+  double acc = 0.0;
+  for (int i = threadIdx.x; i < n; i += REDUCE_THREADS) acc += partials[i];
+  const double t = block_sum_256(acc, sh);
+  if (threadIdx.x == 0) *out = t;
 }
 
 typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
@@ -285,6 +335,8 @@ extern "C" int neptune_rt_finalize(neptune_rt_ctx *c) {
   cudaStreamDestroy(c->h2d_stream);
   cudaStreamDestroy(c->d2h_stream);
   for (cudaEvent_t e : c->ev_pool) cudaEventDestroy(e);
+  if (c->red_partials) cudaFree(c->red_partials);
+  if (c->red_host) cudaFreeHost(c->red_host);
   delete c;
   return NEPTUNE_RT_OK;
 }
@@ -425,6 +477,48 @@ extern "C" int neptune_rt_field_store(neptune_rt_field *dst, neptune_rt_field *s
     box_copy_kernel<float><<<grid, block, 0, c->stream>>>((float *)dst->dptr + doff, (const float *)src->dptr + soff, d_sz, d_sy, s_sz, s_sy, (int)bext[0], (int)bext[1], (int)bext[2]);
   RT_CUDA(c, cudaGetLastError());
   c->launches++;
+  return NEPTUNE_RT_OK;
+}
+
+extern "C" int neptune_rt_field_reduce_sum(neptune_rt_field *f, const int64_t *lb, const int64_t *ub, int allreduce, double *result) {
+  if (!f || !result) return set_error(f ? f->ctx : nullptr, NEPTUNE_RT_EINVAL, "field_reduce_sum: NULL argument");
+  neptune_rt_ctx *c = f->ctx;
+  int64_t blb[3], bext[3], flb[3], tmp[3];
+  canon_box(f->rank, lb ? lb : f->lb, ub ? ub : f->ub, blb, bext);
+  canon_box(f->rank, f->lb, f->ub, flb, tmp);
+  bool empty = false;
+  for (int a = 0; a < 3; ++a) {
+    empty |= bext[a] <= 0;
+    if (bext[a] > 0 && (blb[a] < flb[a] || blb[a] + bext[a] > flb[a] + f->ext[a]))
+      return set_error(c, NEPTUNE_RT_EINVAL, "field_reduce_sum: bounds leave the field's box");
+  }
+  cudaSetDevice(c->device);
+  if (!c->red_partials) {
+    RT_CUDA(c, cudaMalloc(&c->red_partials, sizeof(double) * (REDUCE_BLOCKS + 1)));
+    RT_CUDA(c, cudaMallocHost(&c->red_host, sizeof(double)));
+  }
+  double *out = c->red_partials + REDUCE_BLOCKS;
+  if (empty) {
+    RT_CUDA(c, cudaMemsetAsync(out, 0, sizeof(double), c->stream));
+  } else {
+    const long long sy = f->ext[2], sz = f->ext[1] * f->ext[2];
+    const long long off = (blb[0] - flb[0]) * sz + (blb[1] - flb[1]) * sy + (blb[2] - flb[2]);
+    if (f->dtype == NEPTUNE_RT_F64)
+      reduce_sum_rows<double><<<REDUCE_BLOCKS, REDUCE_THREADS, 0, c->stream>>>((const double *)f->dptr + off, sz, sy, (int)bext[0], (int)bext[1], (int)bext[2], c->red_partials);
+    else
+      reduce_sum_rows<float><<<REDUCE_BLOCKS, REDUCE_THREADS, 0, c->stream>>>((const float *)f->dptr + off, sz, sy, (int)bext[0], (int)bext[1], (int)bext[2], c->red_partials);
+    RT_CUDA(c, cudaGetLastError());
+    reduce_sum_final<<<1, REDUCE_THREADS, 0, c->stream>>>(c->red_partials, REDUCE_BLOCKS, out);
+    RT_CUDA(c, cudaGetLastError());
+    c->launches += 2;
+  }
+  if (allreduce && c->nranks > 1) {
+    if (!c->comm) return set_error(c, NEPTUNE_RT_ENCCL, "field_reduce_sum: no communicator (neptune_rt_comm_init)");
+    RT_NCCL(c, nccl().AllReduce(out, out, 1, ncclDouble, ncclSum, c->comm, c->stream));
+  }
+  RT_CUDA(c, cudaMemcpyAsync(c->red_host, out, sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+  RT_CUDA(c, cudaStreamSynchronize(c->stream));
+  *result = f->dtype == NEPTUNE_RT_F64 ? *c->red_host : (double)(float)*c->red_host;
   return NEPTUNE_RT_OK;
 }
 

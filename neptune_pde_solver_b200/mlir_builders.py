@@ -285,3 +285,34 @@ def laplacian_s_1d(n: int = 16, dxinv2: float = 100.0, ty: str = "f64") -> str:
           "        neptune_ir.yield %%lap_i : %s" % ty,
           "      }"]
     return hdr + "module {\n" + _entry(1, ty, 0, "\n".join(b), ["%u0"]) + "\n}\n"
+
+
+def field_sum(shape: Sequence[int], ty: str = "f64", lb=None, sub_lb=None, sub_ub=None) -> str:
+    """`neptune_ir.reduce` kind "sum" of a whole field or of the sub-box [sub_lb, sub_ub)
+    (`include/Dialect/NeptuneIR/NeptuneIROps.td:264-299`: `reduce %t (in #bounds)? {kind = "sum"}`)."""
+    rank = len(shape)
+    hdr, _, _ = _header(shape, ty, lb)
+    mr = _memref(rank, ty)
+    dom = "" if sub_lb is None else " in " + _bounds(sub_lb, sub_ub)
+    lines = ["  func.func @entry(%%in: %s) -> %s {" % (mr, ty),
+             "    %%fin = neptune_ir.wrap %%in : %s -> !field" % mr,
+             "    %u0  = neptune_ir.load %fin : !field -> !temp",
+             '    %%s   = neptune_ir.reduce %%u0%s {kind = "sum"} : !temp -> %s' % (dom, ty),
+             "    func.return %%s : %s" % ty,
+             "  }"]
+    return hdr + "module {\n" + "\n".join(lines) + "\n}\n"
+
+
+def heat_star_then_sum(shape: Sequence[int], alpha: float, ty: str = "f64") -> str:
+    """One heat step stored to %out, then the sum of the new state over the interior: the
+    "sweep, then a norm-like scalar" shape of a convergence check."""
+    text = heat_star(shape, alpha, ty)
+    rank = len(shape)
+    mr = _memref(rank, ty)
+    ilb, iub = [1] * rank, [int(n) - 1 for n in shape]
+    text = text.replace("(%%out: %s, %%in: %s) -> %s {" % (mr, mr, mr), "(%%out: %s, %%in: %s) -> %s {" % (mr, mr, ty))
+    tail_old = "    %%res = neptune_ir.unwrap %%fout : !field -> %s\n    func.return %%res : %s" % (mr, mr)
+    tail_new = ('    %%s = neptune_ir.reduce %%r in %s {kind = "sum"} : !temp -> %s\n'
+                "    func.return %%s : %s") % (_bounds(ilb, iub), ty, ty)
+    assert tail_old in text
+    return text.replace(tail_old, tail_new)

@@ -86,6 +86,7 @@ def lib() -> C.CDLL:
         "neptune_rt_field_device_ptr": (vp, [vp]),
         "neptune_rt_field_bytes": (i64, [vp]),
         "neptune_rt_field_store": (i32, [vp, vp, i64p, i64p]),
+        "neptune_rt_field_reduce_sum": (i32, [vp, i64p, i64p, i32, C.POINTER(C.c_double)]),
         "neptune_rt_body_key": (C.c_uint64, [C.POINTER(StencilDescC)]),
         "neptune_rt_body_compiled": (i32, [C.c_uint64]),
         "neptune_rt_stencil_create": (i32, [vp, C.POINTER(StencilDescC), C.POINTER(vp)]),
@@ -117,6 +118,7 @@ def lib() -> C.CDLL:
         "neptune_b200_apply_stencil": (vp, [vp, vp, i32]),
         "neptune_b200_apply_cuda_source": (C.c_char_p, [vp, i32]),
         "neptune_b200_run_host": (i32, [vp, vp, C.c_char_p, i32, C.POINTER(vp)]),
+        "neptune_b200_last_scalars": (i32, [vp, C.POINTER(C.c_double), i32]),
         "neptune_b200_run_steps_host": (i32, [vp, vp, C.c_char_p, i32, C.POINTER(vp), i64, C.POINTER(i32)]),
     }
     for name, (res, args) in sig.items():
@@ -319,6 +321,13 @@ class Field:
             rc = self.ctx._L.neptune_rt_field_store(self.h, src.h, _i64(lb), _i64(ub))
         self.ctx._check(rc)
 
+    def reduce_sum(self, lb=None, ub=None, allreduce: bool = False) -> float:
+        """`neptune_ir.reduce` kind="sum" over [lb, ub) (None = whole box); tolerance tier (fp64 tree sum)."""
+        r = C.c_double()
+        self.ctx._check(self.ctx._L.neptune_rt_field_reduce_sum(
+            self.h, None if lb is None else _i64(lb), None if ub is None else _i64(ub), int(allreduce), C.byref(r)))
+        return r.value
+
     def device_ptr(self) -> int:
         return int(self.ctx._L.neptune_rt_field_device_ptr(self.h) or 0)
 
@@ -451,6 +460,12 @@ class Module:
     def run(self, ctx: Context, function: str, args: Sequence[np.ndarray]):
         """One call of the compiled entry on host memrefs (in place, like the reference's driver)."""
         self._check(self._L.neptune_b200_run_host(self.h, ctx.h, function.encode(), len(args), self._ptrs(args)))
+        n = self._L.neptune_b200_last_scalars(self.h, None, 0)
+        if n <= 0:
+            return []
+        buf = (C.c_double * n)()
+        self._L.neptune_b200_last_scalars(self.h, buf, n)
+        return list(buf)
 
     def run_steps(self, ctx: Context, function: str, args: Sequence[np.ndarray], nsteps: int) -> int:
         """`for step: entry(out, in, extra...); swap(out, in)` resident on the device.

@@ -115,7 +115,12 @@ def emit_module(mod: ms.Module) -> str:
         for _, ty in fn.args:
             elem = ty.elem
         T = _CT[elem]
-        sig = "%s *%s(%s)" % (T, cname, ", ".join("%s *%s" % (T, _sym(a)) for a, _ in fn.args))
+        # a function whose return operand is a `reduce` result returns the scalar by value
+        scalars = {op.results[0] for op in fn.ops if op.name == "reduce"}
+        rets = [op for op in fn.ops if op.name == "return"]
+        scalar_ret = bool(rets and rets[0].operands and rets[0].operands[0] in scalars)
+        sig = "%s %s%s(%s)" % (T, "" if scalar_ret else "*", cname,
+                               ", ".join("%s *%s" % (T, _sym(a)) for a, _ in fn.args))
         protos.append(sig + ";")
         L = [sig + " {"]
         frees: List[str] = []
@@ -150,6 +155,24 @@ def emit_module(mod: ms.Module) -> str:
                     for d in range(rank):
                         ind = ind[:-2]
                         L.append(ind + "}")
+            elif op.name == "reduce":
+                # ReduceLowering / buildReduceLoops (DataflowLowering.cpp:589-698): acc = 0, then one
+                # scf.for per dimension carrying acc, innermost `acc = acc + load` in the element type
+                if op.callee != "sum":
+                    raise NotImplementedError("reduce kind %r" % op.callee)
+                sb = op.types[0].bounds
+                dom = op.bounds if op.bounds is not None else sb
+                acc = _sym(op.results[0])
+                L.append("  %s %s = 0;" % (T, acc))
+                ind = "  "
+                for d in range(sb.rank):
+                    L.append("%sfor (long i%d = %d; i%d < %d; ++i%d) {" % (ind, d, dom.lb[d], d, dom.ub[d], d))
+                    ind += "  "
+                si = ["i%d - (%d)" % (d, sb.lb[d]) for d in range(sb.rank)]
+                L.append("%s%s = %s + %s[%s];" % (ind, acc, acc, _sym(op.operands[0]), _lin(si, sb.shape)))
+                for d in range(sb.rank):
+                    ind = ind[:-2]
+                    L.append(ind + "}")
             elif op.name == "constant":
                 pass
             elif op.name == "return":
@@ -217,6 +240,13 @@ class CompiledModule:
         fn.argtypes = [ctypes.c_void_p] * len(args)
         for a in args:
             assert a.flags["C_CONTIGUOUS"]
+        return fn(*[a.ctypes.data for a in args])
+
+    def call_scalar(self, name: str, args: Sequence[np.ndarray]) -> float:
+        """Call a function that returns a `reduce` result by value."""
+        fn = getattr(self.lib, "nep_" + name[1:])
+        fn.restype = ctypes.c_double if args[0].dtype == np.float64 else ctypes.c_float
+        fn.argtypes = [ctypes.c_void_p] * len(args)
         return fn(*[a.ctypes.data for a in args])
 
     def run_steps(self, u: np.ndarray, extra: Sequence[np.ndarray], nsteps: int, entry="@entry") -> np.ndarray:

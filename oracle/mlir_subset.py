@@ -375,6 +375,16 @@ class _Parser:
                 while self.accept(","):
                     tys.append(self.parse_type())
             return HostOp("return", (), tuple(ops))
+        if op == "neptune_ir.reduce":        # include/Dialect/NeptuneIR/NeptuneIROps.td:272-299
+            src = self.next()[1]
+            b = None
+            if self.accept("in"):
+                b = self.parse_bounds()
+            kind = None
+            if self.accept("{"):
+                self.expect("kind"); self.expect("="); kind = self.next()[1].strip('"'); self.expect("}")
+            self.expect(":"); t0 = self.parse_type(); self.expect("->"); t1 = self.parse_type()
+            return HostOp("reduce", results, (src,), (t0, t1), callee=kind, bounds=b)
         if op == "neptune_ir.apply":
             return HostOp("apply", results, apply=self.parse_apply(results[0]))
         if op == "arith.constant":          # host-level scalars (e.g. dt) never reach the sweep

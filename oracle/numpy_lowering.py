@@ -101,6 +101,18 @@ def run_function(mod: ms.Module, name: str, args: Sequence[np.ndarray]) -> List[
                 ssl = tuple(slice(l - b, u - b) for l, u, b in zip(op.bounds.lb, op.bounds.ub, slb))
                 dsl = tuple(slice(l - b, u - b) for l, u, b in zip(op.bounds.lb, op.bounds.ub, dlb))
                 dst[dsl] = src[ssl]
+        elif op.name == "reduce":
+            # ReduceLowering (lib/Passes/DataflowLowering.cpp:589-698): only kind "sum"; acc starts at
+            # zero and every element of the domain is added in row-major order, in the element type.
+            # np.cumsum accumulates strictly left to right in the array's dtype (np.sum is pairwise).
+            if op.callee != "sum":
+                raise NotImplementedError('reduce kind %r (the reference lowers only "sum", :655-657)' % op.callee)
+            src = env[op.operands[0]]
+            ty = op.types[0]
+            b = op.bounds if op.bounds is not None else ty.bounds
+            sl = tuple(slice(l - o, u - o) for l, u, o in zip(b.lb, b.ub, ty.bounds.lb))
+            flat = np.ascontiguousarray(src[sl]).reshape(-1)
+            env[op.results[0]] = np.cumsum(flat, dtype=src.dtype)[-1] if flat.size else src.dtype.type(0)
         elif op.name == "constant":
             pass
         elif op.name == "return":

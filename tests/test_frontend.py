@@ -145,3 +145,20 @@ def test_no_gpu_means_loud_failure(nb):
     with pytest.raises(nb.NeptuneError) as e:
         nb.Context(0)
     assert "no CPU fallback" in str(e.value)
+
+
+def test_reduce_is_planned_and_other_kinds_rejected(nb):
+    """`neptune_ir.reduce` (NeptuneIROps.td:264-299): kind "sum" becomes neptune_rt_field_reduce_sum;
+    the kinds the reference does not lower (DataflowLowering.cpp:655-657) are diagnosed, not guessed."""
+    m = nb.Module(H.mb.field_sum([8, 8, 8], "f32", lb=[1, 2, 3], sub_lb=[2, 2, 4], sub_ub=[5, 9, 10]))
+    plan = m.plan("@entry")
+    assert "neptune_rt_field_reduce_sum([2,2,4]..[5,9,10])" in plan and "arg 0 %in: upload, no download" in plan
+    assert m.apply_count() == 0
+    m.destroy()
+    m = nb.Module(H.mb.heat_star_then_sum([8, 8, 8], 0.1))
+    plan = m.plan("@entry")
+    assert "neptune_rt_apply" in plan and "neptune_rt_field_reduce_sum([1,1,1]..[7,7,7])" in plan
+    m.destroy()
+    with pytest.raises(nb.NeptuneError) as e:
+        nb.Module(H.mb.field_sum([8, 8], "f64").replace('"sum"', '"l2"'))
+    assert "EUNSUPPORTED" in str(e.value) and "l2" in str(e.value)

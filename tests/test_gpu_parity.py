@@ -409,3 +409,60 @@ def test_entry_on_host_memrefs_pipelines_at_size(nb, ctx):
         assert H.bits_equal(out, want)
     finally:
         m.destroy()
+
+
+@pytest.mark.parametrize("ty", ["f64", "f32"])
+def test_reduce_sum_tolerance_tier(nb, ctx, ty):
+    """`neptune_ir.reduce` kind "sum" (DataflowLowering.cpp:589-698).  The reference adds strictly left
+    to right; the device sum is a fixed-partition fp64 tree, so parity is the tolerance tier, with the
+    bound written here: |gpu - ref| <= n * eps(elem) * sum|x| (the classical bound on the REFERENCE's
+    own rounding error; the fp64 tree is far inside it).  Deterministic run to run."""
+    from oracle import mlir_subset as ms, numpy_lowering as onp
+    dt = np.float64 if ty == "f64" else np.float32
+    shape = (40, 33, 130)
+    u = np.random.default_rng(21).uniform(-1, 1, size=shape).astype(dt)
+    for kw in ({}, {"lb": [2, 3, 4], "sub_lb": [3, 3, 5], "sub_ub": [41, 30, 131]}):
+        text = H.mb.field_sum(list(shape), ty, **kw)
+        want = float(onp.run_function(ms.parse(text), "@entry", [u])[0])
+        m = nb.Module(text)
+        try:
+            got = m.run(ctx, "@entry", [u])
+            again = m.run(ctx, "@entry", [u])
+        finally:
+            m.destroy()
+        assert len(got) == 1 and got == again
+        sub = u if not kw else u[1:39, 0:27, 1:127]
+        bound = sub.size * float(np.finfo(dt).eps) * float(np.sum(np.abs(sub), dtype=np.float64))
+        assert abs(got[0] - want) <= bound, (got[0], want, bound)
+        # and against an exactly rounded sum the fp64 tree is within a few ulps of the result type
+        exact = float(np.sum(sub.astype(np.longdouble)))
+        assert abs(got[0] - exact) <= 4 * float(np.finfo(dt).eps) * max(1.0, abs(exact)) + (1e-9 if ty == "f64" else 0.0)
+    # API level: empty box sums to zero, out-of-box bounds are an error, ones sum to the point count
+    f = nb.Field.from_numpy(ctx, np.ones(shape, dtype=dt))
+    try:
+        assert f.reduce_sum() == float(np.prod(shape))
+        assert f.reduce_sum([5, 5, 5], [5, 9, 9]) == 0.0
+        assert f.reduce_sum([1, 2, 3], [4, 5, 6]) == 27.0
+        with pytest.raises(nb.NeptuneError):
+            f.reduce_sum([0, 0, 0], [41, 33, 130])
+    finally:
+        f.free()
+
+
+def test_sweep_then_reduce_program_on_device(nb, ctx):
+    """apply -> store -> reduce of the new state: the field is bit-exact, the scalar within the bound."""
+    from oracle import mlir_subset as ms, numpy_lowering as onp
+    shape = (24, 40, 136)
+    text = H.mb.heat_star_then_sum(list(shape), 0.1)
+    u, _ = H.inputs(shape, 0, "f64", seed=31)
+    want_out = np.zeros_like(u)
+    want_s = float(onp.run_function(ms.parse(text), "@entry", [want_out, u.copy()])[0])
+    m = nb.Module(text)
+    try:
+        out = np.zeros_like(u)
+        got = m.run(ctx, "@entry", [out, u.copy()])
+    finally:
+        m.destroy()
+    assert H.bits_equal(out, want_out)
+    inner = want_out[1:-1, 1:-1, 1:-1]
+    assert abs(got[0] - want_s) <= inner.size * 2.2e-16 * float(np.sum(np.abs(inner)))

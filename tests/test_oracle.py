@@ -79,3 +79,38 @@ def test_golden_vectors():
         extra = [g["extra%d" % k] for k in range(int(g["n_extra"]))]
         got = onp.run_steps(ms.parse(text), g["u0"], extra, int(g["steps"]))
         assert H.bits_equal(got, g["result"]), f
+
+
+@pytest.mark.parametrize("ty", ["f64", "f32"])
+def test_reduce_sum_is_a_strict_left_fold(ty):
+    """`neptune_ir.reduce` kind "sum" (lib/Passes/DataflowLowering.cpp:589-698): acc = 0, then
+    acc = acc + x in row-major order, in the element type.  numpy (cumsum) and gcc restatements
+    agree bit for bit, on the whole box and on a sub-box of a non-zero-based field."""
+    dt = np.float64 if ty == "f64" else np.float32
+    u = np.random.default_rng(5).uniform(-1, 1, size=(9, 12, 14)).astype(dt)
+    for kw in ({}, {"lb": [2, 3, 4], "sub_lb": [3, 3, 5], "sub_ub": [9, 14, 17]}):
+        text = H.mb.field_sum(list(u.shape), ty, **kw)
+        got_np = onp.run_function(ms.parse(text), "@entry", [u])[0]
+        got_c = oc.CompiledModule(text, tag="t_reduce_%s" % ty).call_scalar("@entry", [u])
+        assert dt(got_c) == got_np and got_np.dtype == dt
+        # by hand: python floats are f64, so only check the f64 case against a plain loop
+        if ty == "f64":
+            sub = u if not kw else u[1:7, 0:11, 1:13]
+            acc = 0.0
+            for v in sub.reshape(-1):
+                acc = acc + float(v)
+            assert acc == float(got_np)
+    ones = np.ones((9, 12, 14), dtype=dt)
+    assert onp.run_function(ms.parse(H.mb.field_sum([9, 12, 14], ty)), "@entry", [ones])[0] == 9 * 12 * 14
+    with pytest.raises(NotImplementedError):
+        onp.run_function(ms.parse(H.mb.field_sum([4, 4], ty).replace('"sum"', '"max"')), "@entry", [ones[0, :4, :4].copy()])
+
+
+def test_sweep_then_reduce_program():
+    text = H.mb.heat_star_then_sum([9, 12, 14], 0.1)
+    u, _ = H.inputs((9, 12, 14), 0, "f64", seed=8)
+    o1, o2 = np.zeros_like(u), np.zeros_like(u)
+    s1 = onp.run_function(ms.parse(text), "@entry", [o1, u])[0]
+    s2 = oc.CompiledModule(text, tag="t_sweep_reduce").call_scalar("@entry", [o2, u])
+    assert H.bits_equal(o1, o2) and float(s1) == s2
+    assert H.bits_equal(o1, H.oracle_entry(H.mb.heat_star([9, 12, 14], 0.1), u, []))
