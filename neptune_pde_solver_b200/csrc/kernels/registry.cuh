@@ -8,6 +8,7 @@
 #include "sweep_tma.cuh"
 #include "sweep_tb2.cuh"
 #include "sweep_tb2m.cuh"
+#include "sweep_rows.cuh"
 
 namespace neptune {
 
@@ -98,9 +99,10 @@ template <class F, class C, bool FMA> int launch_tma(const SweepArgs &a) {
 
 template <class F, class C, bool FMA, bool MARCH = false> int launch_tb2(const SweepArgs &a) {
   typedef typename std::conditional<MARCH, Tb2mGeom<F, C>, Tb2Geom<F, C>>::type G;
-  void (*kernel)(const KParams<F>, const CUtensorMap);
-  if constexpr (MARCH) kernel = sweep_tb2m<F, C, FMA>;
-  else kernel = sweep_tb2<F, C, FMA>;
+  auto kernel = [] {
+    if constexpr (MARCH) return sweep_tb2m<F, C, FMA>;
+    else return sweep_tb2<F, C, FMA>;
+  }();
   static int occ_cached[16] = {0};
   int dev = 0;
   cudaGetDevice(&dev);
@@ -131,8 +133,61 @@ template <class F, class C, bool FMA, bool MARCH = false> int launch_tb2(const S
   if (items > 0x7fffffffLL) return (int)cudaErrorInvalidConfiguration;
   p.nitems = (int)items;
   const int grid = (int)std::min<long long>(items, slots);
-  kernel<<<grid, G::THREADS, G::SMEM_BYTES, a.stream>>>(p, *a.tmap);
+  if constexpr (MARCH) {
+    if (F::NIN > 1 && !a.tmap_pw) return (int)cudaErrorInvalidValue;
+    kernel<<<grid, G::THREADS, G::SMEM_BYTES, a.stream>>>(p, *a.tmap, a.tmap_pw ? *a.tmap_pw : *a.tmap);
+  } else {
+    kernel<<<grid, G::THREADS, G::SMEM_BYTES, a.stream>>>(p, *a.tmap);
+  }
   return (int)cudaGetLastError();
+}
+
+// rank-2 row marching (sweep_rows.cuh): work item = (row chunk, strip of TX columns)
+template <class F, class C, bool FMA> int launch_rows(const SweepArgs &a) {
+  typedef RowGeom<F, C> G;
+  auto kernel = sweep_rows<F, C, FMA>;
+  static int occ_cached[16] = {0};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (dev < 0 || dev >= 16) dev = 0;
+  if (occ_cached[dev] == 0) {
+    cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, G::SMEM_BYTES);
+    if (e != cudaSuccess) return (int)e;
+    int occ = 0;
+    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kernel, G::THREADS, G::SMEM_BYTES);
+    if (e != cudaSuccess) return (int)e;
+    if (occ < 1) return (int)cudaErrorLaunchOutOfResources;
+    occ_cached[dev] = occ;
+  }
+  KParams<F> p;
+  fill_params<F>(p, a);
+  const int wy = a.whi[1] - a.wlo[1];
+  if (wy <= 0 || a.whi[2] <= a.wlo[2]) return 0;
+  p.cxo = a.wlo[2] / C::TX;
+  p.ncx = (a.whi[2] + C::TX - 1) / C::TX - p.cxo;
+  p.ncy = 1;
+  const int slots = a.sm_count * occ_cached[dev];
+  p.zchunk = a.zchunk > 0 ? std::min(a.zchunk, wy) : choose_zchunk(wy, p.ncx, slots, 1);
+  p.nchunks = (wy + p.zchunk - 1) / p.zchunk;
+  const long long items = (long long)p.nchunks * p.ncx;
+  if (items > 0x7fffffffLL) return (int)cudaErrorInvalidConfiguration;
+  p.nitems = (int)items;
+  const int grid = (int)std::min<long long>(items, slots);
+  kernel<<<grid, G::THREADS, G::SMEM_BYTES, a.stream>>>(p);
+  return (int)cudaGetLastError();
+}
+
+template <class F, class C, bool FMA> Variant rows_variant(const char *name) {
+  typedef RowGeom<F, C> G;
+  Variant v;
+  v.name = name;
+  v.kind = VARIANT_ROWS;
+  v.fma = FMA;
+  v.tx = C::TX; v.ty = C::RB;
+  v.halo_x = G::HX; v.halo_y = 1;
+  v.threads = G::THREADS; v.smem = G::SMEM_BYTES;
+  v.launch = &launch_rows<F, C, FMA>;
+  return v;
 }
 
 template <class F, class C, bool FMA, bool MARCH = false> Variant tb2_variant(const char *name) {
@@ -177,7 +232,15 @@ typedef Tb2Cfg<64, 32, 4, 5, 1> Tb2D;
 typedef Tb2Cfg<128, 14, 2, 6, 1> Tb2mA;
 typedef Tb2Cfg<64, 16, 2, 6, 2> Tb2mB;
 typedef Tb2Cfg<128, 14, 2, 8, 1> Tb2mC;
+// 512 threads = 4 warps per SM sub-partition -> up to 128 registers (5 warps per sub-partition: 96)
+typedef Tb2Cfg<64, 24, 2, 8, 1> Tb2mD;
+typedef Tb2Cfg<128, 10, 2, 6, 1> Tb2mE;
+typedef Tb2Cfg<64, 24, 2, 5, 1> Tb2mG;
+typedef Tb2Cfg<128, 14, 2, 4, 1> Tb2mF;   // two staged tiles per slot: four slots fit beside the level-1 planes
 typedef TileCfg<64, 8, 1, 6, 1> Tile3W;   // many-input bodies (one coefficient field per tap)
+typedef RowCfg<512, 4, 4, 3> Rows512;     // strip of 512 columns (elements = TX), 4 rows per stage, ring of 4
+typedef RowCfg<256, 8, 4, 4> Rows256;
+typedef RowCfg<1024, 2, 6, 1> Rows1024;
 typedef TileCfg<128, 32, 8, 3, 2> Tile2A;
 typedef TileCfg<128, 16, 4, 4, 2> Tile2B;
 typedef TileCfg<64, 64, 8, 3, 2> Tile2C;
@@ -215,9 +278,22 @@ template <class F> struct BodyRegistrar {
             e.variants.push_back(tb2_variant<F, Tb2mA, true, true>("tb2m:128x14"));
             e.variants.push_back(tb2_variant<F, Tb2mB, false, true>("tb2m:64x16"));
             e.variants.push_back(tb2_variant<F, Tb2mC, false, true>("tb2m:128x14n8"));
+            e.variants.push_back(tb2_variant<F, Tb2mD, false, true>("tb2m:64x24"));
           }
+        } else if constexpr (F::NIN == 2 && F::RZ == 1 && F::ZSTAR) {
+          // input 0 plus pointwise inputs (Jacobi with a right-hand side): the z-marching form only
+          e.variants.push_back(tb2_variant<F, Tb2mG, false, true>("tb2m:64x24"));
+          e.variants.push_back(tb2_variant<F, Tb2mG, true, true>("tb2m:64x24"));
+          e.variants.push_back(tb2_variant<F, Tb2mE, false, true>("tb2m:128x10"));
+          e.variants.push_back(tb2_variant<F, Tb2mF, false, true>("tb2m:128x14"));
         }
       } else {
+        if constexpr (F::RANK == 2 && F::RY == 1 && F::NIN <= 4) {
+          e.variants.push_back(rows_variant<F, Rows512, false>("rows:512"));
+          e.variants.push_back(rows_variant<F, Rows512, true>("rows:512"));
+          e.variants.push_back(rows_variant<F, Rows256, false>("rows:256"));
+          e.variants.push_back(rows_variant<F, Rows1024, false>("rows:1024"));
+        }
         e.variants.push_back(tma_variant<F, Tile2A, false>("tma:128x32"));
         e.variants.push_back(tma_variant<F, Tile2A, true>("tma:128x32"));
         e.variants.push_back(tma_variant<F, Tile2B, false>("tma:128x16"));

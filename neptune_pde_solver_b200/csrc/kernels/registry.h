@@ -28,12 +28,13 @@ struct SweepArgs {
   int sm_count = 148;
   cudaStream_t stream = nullptr;
   const CUtensorMap *tmap = nullptr;  // tensor map of the staged input (TMA variants)
+  const CUtensorMap *tmap_pw = nullptr;  // tensor map of the pointwise input (two-input temporally blocked kernels)
 };
 
-enum VariantKind { VARIANT_DIRECT = 0, VARIANT_TMA = 1, VARIANT_TB2 = 2 };
+enum VariantKind { VARIANT_DIRECT = 0, VARIANT_TMA = 1, VARIANT_TB2 = 2, VARIANT_ROWS = 3 };
 
 struct Variant {
-  std::string name;     // "direct", "tma:64x16", ...
+  std::string name;     // "direct", "tma:64x16", "tb2m:128x14", "rows:512", ...
   int kind = VARIANT_DIRECT;
   bool fma = false;
   int tx = 0, ty = 0;           // tile (TMA)

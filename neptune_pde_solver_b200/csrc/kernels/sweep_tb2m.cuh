@@ -39,29 +39,38 @@ template <class F, class C> struct Tb2mGeom {
   static constexpr int BOX_Y = C::TY + 4;
   static constexpr int STAGE_TX_BYTES = P0 * BOX_Y * S;
   static constexpr int STAGE_BYTES = (STAGE_TX_BYTES + 127) / 128 * 128;
+  static constexpr int NSTG = F::NIN;                      // staged tiles per ring slot: input 0, then the pointwise inputs
+  static constexpr int SLOT_BYTES = NSTG * STAGE_BYTES;
   static constexpr int GUARD_BYTES = (P0 * S * (VY > 2 ? VY - 1 : 1) + 127) / 128 * 128;
   static constexpr int P1 = NBX * VX, H1 = NBY * VY;  // level-1 plane
   static constexpr int L1_BYTES = (P1 * H1 * S + 127) / 128 * 128;
   static constexpr int L1_GUARD = (P1 * S + 127) / 128 * 128;  // row -1 of the top ring blocks
   static constexpr int NL1 = 2;
-  static constexpr int SMEM_BYTES = GUARD_BYTES + NS * STAGE_BYTES + GUARD_BYTES + L1_GUARD + NL1 * L1_BYTES + L1_GUARD +
+  static constexpr int SMEM_BYTES = GUARD_BYTES + NS * SLOT_BYTES + GUARD_BYTES + L1_GUARD + NL1 * L1_BYTES + L1_GUARD +
                                     2 * NS * 8 + 128;
   static_assert(F::RZ == 1 && F::RY <= 1 && F::RX <= 1 && F::ZSTAR, "z-marching needs a radius-1 body with centre-column z taps");
-  static_assert(F::NIN == 1 && F::STAGED == 0, "temporal blocking needs a single input");
+  static_assert(F::STAGED == 0, "input 0 must be the only input read at neighbour offsets (the others are pointwise)");
+  static_assert(F::NIN <= 2, "one pointwise input at most (its tiles share the ring slots)");
+  static_assert(SMEM_BYTES <= 227 * 1024, "ring does not fit in shared memory");
   static_assert(C::TX % VX == 0 && C::TY % VY == 0, "tile must be a multiple of the thread block");
   static_assert(P0 <= 256 && BOX_Y <= 256, "TMA box dimensions are limited to 256 elements");
   static_assert(THREADS <= 1024, "too many threads");
 };
 
-// accessor: centre-plane window c[][], centre blocks m[][] (plane below) and p[][] (plane above)
+// accessor: centre-plane window c[][], centre blocks m[][] (plane below) and p[][] (plane above) of
+// input 0; pw[][][] = the pointwise inputs (coefficients, right-hand sides) at the thread's own points
 template <class F, int VY, int VX, int IY, int IX> struct MarchAcc {
   typedef typename F::T T;
+  static constexpr int NPW = F::NIN > 1 ? F::NIN - 1 : 1;
   const T (&m)[VY][VX];
   const T (&c)[VY + 2][VX + 2];
   const T (&p)[VY][VX];
+  const T (&pw)[NPW][VY][VX];
   template <int K, int DZ, int DY, int DX> __device__ __forceinline__ T tap() const {
-    static_assert(K == 0, "single input");
-    if constexpr (DZ == 0) {
+    if constexpr (K != 0) {
+      static_assert(DZ == 0 && DY == 0 && DX == 0, "inputs other than input 0 are read at offset 0 only");
+      return pw[K - 1][IY][IX];
+    } else if constexpr (DZ == 0) {
       return c[IY + DY + 1][IX + DX + 1];
     } else {
       static_assert(DY == 0 && DX == 0, "z taps sit on the centre column");
@@ -98,16 +107,17 @@ __device__ __forceinline__ void load_halo(T (&c)[VY + 2][VX + 2], const T *blk, 
 
 template <class F, class C, bool FMA>
 __global__ void __launch_bounds__((Tb2mGeom<F, C>::THREADS), C::MINB)
-sweep_tb2m(const __grid_constant__ KParams<F> p, const __grid_constant__ CUtensorMap tmap) {
+sweep_tb2m(const __grid_constant__ KParams<F> p, const __grid_constant__ CUtensorMap tmap, const __grid_constant__ CUtensorMap tmap_pw) {
   typedef Tb2mGeom<F, C> G;
   typedef typename F::T T;
   constexpr int VX = G::VX, VY = G::VY, NS = G::NS;
   constexpr int NCW = G::CONSUMERS / 32;
+  constexpr int NPW = F::NIN > 1 ? F::NIN - 1 : 1;
 
   extern __shared__ __align__(128) unsigned char smem_raw[];
   unsigned char *smem = smem_raw + ((128u - (smem_u32(smem_raw) & 127u)) & 127u);
   unsigned char *l0 = smem + G::GUARD_BYTES;                                          // NS level-0 stages
-  unsigned char *l1 = l0 + NS * G::STAGE_BYTES + G::GUARD_BYTES + G::L1_GUARD;         // 2 level-1 planes
+  unsigned char *l1 = l0 + NS * G::SLOT_BYTES + G::GUARD_BYTES + G::L1_GUARD;          // 2 level-1 planes
   const uint32_t full0 = smem_u32(l1 + G::NL1 * G::L1_BYTES + G::L1_GUARD);
   const uint32_t empty0 = full0 + 8 * NS;
   const uint32_t stage0 = smem_u32(l0);
@@ -143,8 +153,10 @@ sweep_tb2m(const __grid_constant__ KParams<F> p, const __grid_constant__ CUtenso
         for (int j = 0; j < nslots; ++j, ++n) {
           const unsigned s = n % NS;
           mbar_wait(empty0 + 8 * s, ((n / NS) & 1) ^ 1);
-          mbar_expect_tx(full0 + 8 * s, G::STAGE_TX_BYTES);
-          tma_load_3d(stage0 + s * G::STAGE_BYTES, &tmap, x0 - 2 * VX, y0 - 2, zb - 2 + j, full0 + 8 * s);
+          mbar_expect_tx(full0 + 8 * s, G::NSTG * G::STAGE_TX_BYTES);
+          tma_load_3d(stage0 + s * G::SLOT_BYTES, &tmap, x0 - 2 * VX, y0 - 2, zb - 2 + j, full0 + 8 * s);
+          if constexpr (F::NIN > 1)   // the pointwise input's tile of the same plane, same box (out-of-box elements arrive as zeros)
+            tma_load_3d(stage0 + s * G::SLOT_BYTES + G::STAGE_BYTES, &tmap_pw, x0 - 2 * VX, y0 - 2, zb - 2 + j, full0 + 8 * s);
         }
       }
     }
@@ -166,7 +178,8 @@ sweep_tb2m(const __grid_constant__ KParams<F> p, const __grid_constant__ CUtenso
   const bool swap = ((tid >> 3) & 1) != 0;
   const T *const ring0 = reinterpret_cast<const T *>(l0);
   T *const ring1 = reinterpret_cast<T *>(l1);
-  constexpr int STAGE_ELEMS = G::STAGE_BYTES / (int)sizeof(T);
+  constexpr int STAGE_ELEMS = G::STAGE_BYTES / (int)sizeof(T);   // offset of the pointwise tile inside a slot
+  constexpr int SLOT_ELEMS = G::SLOT_BYTES / (int)sizeof(T);
   constexpr int L1_ELEMS = G::L1_BYTES / (int)sizeof(T);
   const int soff0 = (by * VY - VY + 2) * G::P0 + VX + bx * VX;   // thread block's first point inside a level-0 stage
   const int soff1 = (by * VY) * G::P1 + bx * VX;                 // ... inside a level-1 plane
@@ -179,6 +192,18 @@ sweep_tb2m(const __grid_constant__ KParams<F> p, const __grid_constant__ CUtenso
   for (int iy = 0; iy < VY; ++iy)
 #pragma unroll
     for (int ix = 0; ix < VX; ++ix) am[iy][ix] = ac[iy][ix] = bm[iy][ix] = bc[iy][ix] = T(0);
+  // pointwise input at the thread's points: plane k-1 (qc, read this iteration from the tile the TMA
+  // producer stages beside input 0's, used by phase A) and plane k-2 (qm, last iteration's qc, used
+  // by phase B).  It is the same field at both levels: a time loop replaces input 0 only.  (r01: reading
+  // it with __ldg instead left the warps waiting on DRAM latency once per plane: 16 warps per SM,
+  // IPC 1.8, DRAM at 3.8 TB/s, and its halo re-reads missed L2: +12 % DRAM reads.)
+  T qc[NPW][VY][VX], qm[NPW][VY][VX];
+#pragma unroll
+  for (int q = 0; q < NPW; ++q)
+#pragma unroll
+    for (int iy = 0; iy < VY; ++iy)
+#pragma unroll
+      for (int ix = 0; ix < VX; ++ix) qc[q][iy][ix] = qm[q][iy][ix] = T(0);
 
   for (int item = blockIdx.x; item < p.nitems; item += gridDim.x) {
     int zb, ze, y0, x0;
@@ -200,7 +225,7 @@ sweep_tb2m(const __grid_constant__ KParams<F> p, const __grid_constant__ CUtenso
     for (int j = 0; j < nslots; ++j) {
       const int k = zb - 2 + j;  // level-0 plane arriving now
       mbar_wait(full0 + 8 * s, ph);
-      const T *cur = ring0 + s * STAGE_ELEMS + soff0;
+      const T *cur = ring0 + s * SLOT_ELEMS + soff0;
 
       // ---- level-0 reads of this iteration ----------------------------------------------------------
       T ap[VY][VX];                 // level-0 centre block of plane k
@@ -208,7 +233,13 @@ sweep_tb2m(const __grid_constant__ KParams<F> p, const __grid_constant__ CUtenso
       if (active) {
 #pragma unroll
         for (int r = 0; r < VY; ++r) lds_vec<T, VX>(ap[r], cur + r * G::P0);
-        if (j >= 2) load_halo<T, VX, VY, G::P0>(wa, prv, swap);
+        if (j >= 2) {
+          load_halo<T, VX, VY, G::P0>(wa, prv, swap);
+          if constexpr (F::NIN > 1) {   // pointwise input at the thread's points of plane k-1 (phase A; phase B next iteration)
+#pragma unroll
+            for (int r = 0; r < VY; ++r) lds_vec<T, VX>(qc[0][r], prv + STAGE_ELEMS + r * G::P0);
+          }
+        }
       }
       // the level-0 stage of plane k-1 is now in registers as far as this warp needs it
       __syncwarp();
@@ -234,7 +265,7 @@ sweep_tb2m(const __grid_constant__ KParams<F> p, const __grid_constant__ CUtenso
             constexpr int IY = decltype(iyc)::value;
             static_for<VX>([&](auto ixc) {
               constexpr int IX = decltype(ixc)::value;
-              MarchAcc<F, VY, VX, IY, IX> acc{am, wa, ap};
+              MarchAcc<F, VY, VX, IY, IX> acc{am, wa, ap, qc};
               const T v = F::template eval<FMA>(acc, p.c);
               ra[IY][IX] = ((m >> (IY * VX + IX)) & 1u) ? v : ac[IY][IX];
             });
@@ -255,7 +286,7 @@ sweep_tb2m(const __grid_constant__ KParams<F> p, const __grid_constant__ CUtenso
             T res[VX];
             static_for<VX>([&](auto ixc) {
               constexpr int IX = decltype(ixc)::value;
-              MarchAcc<F, VY, VX, IY, IX> acc{bm, wb, ra};
+              MarchAcc<F, VY, VX, IY, IX> acc{bm, wb, ra, qm};
               const T v = F::template eval<FMA>(acc, p.c);
               res[IX] = ((m >> (IY * VX + IX)) & 1u) ? v : bc[IY][IX];
             });
@@ -275,6 +306,14 @@ sweep_tb2m(const __grid_constant__ KParams<F> p, const __grid_constant__ CUtenso
         for (int iy = 0; iy < VY; ++iy)
 #pragma unroll
           for (int ix = 0; ix < VX; ++ix) { bm[iy][ix] = bc[iy][ix]; bc[iy][ix] = ra[iy][ix]; }
+        if constexpr (F::NIN > 1) {
+#pragma unroll
+          for (int q = 0; q < NPW; ++q)
+#pragma unroll
+            for (int iy = 0; iy < VY; ++iy)
+#pragma unroll
+              for (int ix = 0; ix < VX; ++ix) qm[q][iy][ix] = qc[q][iy][ix];
+        }
         ++c1;
       }
 #pragma unroll

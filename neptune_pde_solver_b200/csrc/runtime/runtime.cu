@@ -657,13 +657,17 @@ bool tma_eligible(const neptune_rt_stencil *s, int n_in, neptune_rt_field *const
 // in-bounds point of either level reads outside the box; the reference's own fixtures obey this).
 // In slab mode a dim-0 side that has a neighbour needs two ghost planes instead (level 1 is then
 // evaluated on the first ghost plane from level-0 ghosts, exactly as the neighbour evaluates it).
-bool tb2_eligible(const neptune_rt_stencil *s, neptune_rt_field *a, neptune_rt_field *b, bool slab = false) {
+bool tb2_eligible(const neptune_rt_stencil *s, neptune_rt_field *a, neptune_rt_field *b, bool slab = false,
+                  int n_extra = 0, neptune_rt_field *const *extra = nullptr) {
   bool has = false;
   for (auto &v : s->body->variants) has |= v.kind == neptune::VARIANT_TB2;
   const neptune_rt_stencil_desc &d = s->desc.c;
-  if (!has || d.rank != 3 || d.n_inputs != 1) return false;
-  neptune_rt_field *in1[1] = {a};
-  if (!tma_eligible(s, 1, in1, b) || encode_tiled() == nullptr) return false;
+  // inputs beyond input 0 are pointwise (the body registers a tb2 kernel only then) and stay the same
+  // fields at both levels: a time loop replaces input 0 only
+  if (!has || d.rank != 3 || d.n_inputs != 1 + n_extra) return false;
+  neptune_rt_field *inN[NEPTUNE_RT_MAX_INPUTS] = {a};
+  for (int k = 0; k < n_extra; ++k) inN[k + 1] = extra[k];
+  if (!tma_eligible(s, 1 + n_extra, inN, b) || encode_tiled() == nullptr) return false;
   for (int x = 0; x < 3; ++x)
     if (d.ub[x] <= d.lb[x]) return false;
   for (int x = slab ? 1 : 0; x < 3; ++x)
@@ -754,7 +758,7 @@ int do_apply(neptune_rt_stencil *s, int n_in, neptune_rt_field *const *in, neptu
     // tb2:128x16 409, tb2:64x16 382 Gupd/s); narrow boxes keep the 64-wide tile so that fewer CTAs idle on a partial column
     if (s->want_tb == "auto") {
       const bool wide = out->ext[2] >= 256;
-      const char *prefer[] = {wide ? "tb2m:128x14" : "tb2:64x16", wide ? "tb2:128x16" : "tb2:64x16"};
+      const char *prefer[] = {n_in > 1 ? "tb2m:64x24" : wide ? "tb2m:128x14" : "tb2:64x16", wide ? "tb2:128x16" : "tb2:64x16"};
       for (const char *name : prefer) {
         for (auto &v : s->body->variants)
           if (v.kind == neptune::VARIANT_TB2 && v.fma == s->fma && v.name == name) { pick = &v; break; }
@@ -768,7 +772,17 @@ int do_apply(neptune_rt_stencil *s, int n_in, neptune_rt_field *const *in, neptu
       for (auto &v : s->body->variants)
         if (v.kind == neptune::VARIANT_TB2 && (s->want_tb == "auto" || v.name == s->want_tb)) { pick = &v; break; }
   } else if (s->want == "auto") {
-    if (tma_ok)
+    // rank 2: the row-marching kernel (sweep_rows.cuh); narrow boxes take the narrower strip so that the
+    // persistent grid has enough (row chunk, strip) items to balance
+    if (tma_ok) {
+      const char *name = out->ext[2] >= 8192 ? "rows:512" : "rows:256";
+      for (auto &v : s->body->variants)
+        if (v.kind == neptune::VARIANT_ROWS && v.fma == s->fma && v.name == name) { pick = &v; break; }
+      if (!pick)
+        for (auto &v : s->body->variants)
+          if (v.kind == neptune::VARIANT_ROWS && v.fma == s->fma) { pick = &v; break; }
+    }
+    if (tma_ok && !pick)
       for (auto &v : s->body->variants)
         if (v.kind == neptune::VARIANT_TMA && v.fma == s->fma) { pick = &v; break; }
     if (!pick)
@@ -780,14 +794,21 @@ int do_apply(neptune_rt_stencil *s, int n_in, neptune_rt_field *const *in, neptu
     if (!pick)
       for (auto &v : s->body->variants)
         if (v.name == s->want) { pick = &v; break; }
-    if (pick && pick->kind == neptune::VARIANT_TMA && !tma_ok)
+    if (pick && (pick->kind == neptune::VARIANT_TMA || pick->kind == neptune::VARIANT_ROWS) && !tma_ok)
       return set_error(c, NEPTUNE_RT_EINVAL, "kernel variant '%s' needs inputs that share the result's box and 16-byte aligned rows", pick->name.c_str());
   }
   if (!pick) return set_error(c, NEPTUNE_RT_EUNSUPPORTED, "no kernel variant '%s' for this body", s->want.c_str());
-  if (pick->kind != neptune::VARIANT_DIRECT) {
+  CUtensorMap tm_staged, tm_pw;   // copies: get_tmap's cache may move its entries on the next call
+  if (pick->kind == neptune::VARIANT_TMA || pick->kind == neptune::VARIANT_TB2) {
     const CUtensorMap *tm = nullptr;
     if (int rc = get_tmap(s, in[s->body->staged]->dptr, in[s->body->staged]->ext, pick->box_x, pick->box_y, &tm)) return rc;
-    a.tmap = tm;
+    tm_staged = *tm;
+    a.tmap = &tm_staged;
+    if (pick->kind == neptune::VARIANT_TB2 && n_in == 2) {   // the pointwise input's tiles ride in the same ring
+      if (int rc = get_tmap(s, in[1]->dptr, in[1]->ext, pick->box_x, pick->box_y, &tm)) return rc;
+      tm_pw = *tm;
+      a.tmap_pw = &tm_pw;
+    }
   }
   cudaSetDevice(c->device);
   const int e = pick->launch(a);
@@ -993,7 +1014,7 @@ extern "C" int neptune_rt_run_steps(neptune_rt_stencil *s, neptune_rt_field *fa,
 
   if (c->nranks == 1 || !c->comm) {
     int64_t t = 0;
-    if (s->tblock != 1 && tb2_eligible(s, cur, nxt))
+    if (s->tblock != 1 && tb2_eligible(s, cur, nxt, false, n_extra, extra))
       for (; t + 2 <= nsteps; t += 2) {  // two steps per launch: reads cur, writes nxt
         ins[0] = cur;
         if (int rc = do_apply(s, d.n_inputs, ins, nxt, 0, n0, c->stream, true)) return rc;
@@ -1021,11 +1042,16 @@ extern "C" int neptune_rt_run_steps(neptune_rt_stencil *s, neptune_rt_field *fa,
   const bool up = c->rank > 0, down = c->rank + 1 < c->nranks;
   const int64_t own_b = up ? ghost : 0, own_e = n0 - (down ? ghost : 0);
   if (own_e - own_b < 2 * ghost) return set_error(c, NEPTUNE_RT_EINVAL, "run_steps: slab of %lld planes is thinner than two halos", (long long)(own_e - own_b));
-  const bool fuse2 = s->tblock != 1 && ghost >= 2 * radius && own_e - own_b >= 4 * radius && tb2_eligible(s, cur, nxt, true);
+  const bool fuse2 = s->tblock != 1 && ghost >= 2 * radius && own_e - own_b >= 4 * radius && tb2_eligible(s, cur, nxt, true, n_extra, extra);
   // every ghost plane of the first input state
   RT_CUDA(c, cudaEventRecord(c->ev_boundary, c->stream));
   RT_CUDA(c, cudaStreamWaitEvent(c->halo_stream, c->ev_boundary, 0));
   if (int rc = neptune_rt_halo_exchange(c, cur, own_b, own_e, ghost, c->halo_stream)) return rc;
+  // a fused pair of steps evaluates level 1 on the first ghost plane, which reads the pointwise
+  // inputs there: bring their ghost planes up to date once (they do not change over the time loop)
+  if (fuse2)
+    for (int k = 0; k < n_extra; ++k)
+      if (int rc = neptune_rt_halo_exchange(c, extra[k], own_b, own_e, ghost, c->halo_stream)) return rc;
   RT_CUDA(c, cudaEventRecord(c->ev_halo, c->halo_stream));
   RT_CUDA(c, cudaStreamWaitEvent(c->stream, c->ev_halo, 0));
   for (int64_t t = 0; t < nsteps;) {

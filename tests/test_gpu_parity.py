@@ -49,9 +49,10 @@ def test_entry_bit_exact_every_variant(nb, ctx, name, rank, ty):
         out, used = _run_entry(nb, ctx, text, u, extra)
         assert H.bits_equal(out, want), "auto variant %s differs on %s" % (used, shape)
         if si == 0 and rank >= 2:
-            assert used.startswith("tma"), "aligned %d-D extents should take the TMA kernel, took %r" % (rank, used)
+            fast = ("rows", "tma") if rank == 2 else ("tma",)   # rank 2 marches down the rows where the body has that kernel
+            assert used.startswith(fast), "aligned %d-D extents should take the staged kernel, took %r" % (rank, used)
         for v in variants:
-            if v.startswith("tma") and si == 1:
+            if v.startswith(("tma", "rows")) and si == 1:
                 continue  # ragged rows are not TMA-eligible (checked in test_errors)
             out, used = _run_entry(nb, ctx, text, u, extra, variant=v)
             assert used == v
@@ -113,6 +114,53 @@ def test_time_loop_bit_exact(nb, ctx, name, shape, ty, steps):
         assert H.bits_equal(r.download(), want)
         for f in [fa, fb] + fx:
             f.free()
+    finally:
+        m.destroy()
+
+
+@pytest.mark.parametrize("name,shape,ty", [
+    ("heat_star", (300, 1040), "f64"),        # three 512-column strips, the last one ragged; several stages per item
+    ("heat_box_2d9", (70, 2056), "f64"),      # corner taps; more strips than rows per chunk
+    ("heat_box_2d9", (1030, 520), "f32"),     # VX = 4
+    ("jacobi_star", (257, 1024), "f64"),      # pointwise right-hand side beside the marched input
+    ("weighted_2d9", (64, 512), "f64"),
+    ("heat_star", (3, 512), "f64"),           # a single interior row
+])
+def test_row_marching_2d_bit_exact(nb, ctx, name, shape, ty):
+    """sweep_rows (rank-2 row marching over bulk-copied row segments) == the oracle, every strip width,
+    whole sweeps, row-range partitions (the slab path) and a 6-step time loop."""
+    text, n_extra = H.program(name, list(shape), ty)
+    u, extra = H.inputs(shape, n_extra, ty, seed=77)
+    want = H.oracle_entry(text, u, extra)
+    want6 = H.oracle_steps(text, u, extra, 6)
+    dt = np.float64 if ty == "f64" else np.float32
+    m = nb.Module(text)
+    try:
+        st = m.stencil(ctx, 0)
+        rows = [v for v in st.variants() if v.startswith("rows")]
+        assert len(rows) >= 3, st.variants()
+        for v in rows:
+            for zc in ("0", "16"):
+                st.set("variant", v)
+                st.set("zchunk", zc)
+                fin = nb.Field.from_numpy(ctx, u)
+                fx = [nb.Field.from_numpy(ctx, e) for e in extra]
+                fout = nb.Field(ctx, dt, [0, 0], list(shape))
+                fout.fill(float("nan"))
+                st.apply([fin] + fx, fout)
+                assert st.variant() == v
+                assert H.bits_equal(fout.download(), want), (v, zc)
+                fout.fill(float("nan"))
+                n = shape[0]
+                cuts = sorted({0, 1, min(7, n), min(8, n), max(n - 1, 0), n})
+                for p0, p1 in zip(cuts[:-1], cuts[1:]):
+                    st.apply([fin] + fx, fout, planes=(p0, p1))
+                assert H.bits_equal(fout.download(), want), (v, zc, "partition")
+                fb = nb.Field.from_numpy(ctx, u)
+                r = st.run_steps(fin, fb, fx, 6)
+                assert H.bits_equal(r.download(), want6), (v, zc, "steps")
+                for f in [fin, fout, fb] + fx:
+                    f.free()
     finally:
         m.destroy()
 
@@ -307,7 +355,7 @@ def test_temporal_blocking_bit_exact(nb, ctx, name, shape, ty, steps):
     try:
         st = m.stencil(ctx, 0)
         ran = []
-        for tbv in ["tb2:64x16", "tb2:64x16n7", "tb2:128x16", "tb2:64x32", "tb2m:128x14", "tb2m:64x16", "tb2m:128x14n8"]:
+        for tbv in ["tb2:64x16", "tb2:64x16n7", "tb2:128x16", "tb2:64x32", "tb2m:128x14", "tb2m:64x16", "tb2m:128x14n8", "tb2m:64x24"]:
             try:
                 st.set("variant", tbv)
             except nb.NeptuneError:
@@ -323,7 +371,7 @@ def test_temporal_blocking_bit_exact(nb, ctx, name, shape, ty, steps):
             if steps >= 2 and steps % 2 == 0:
                 assert st.variant() == tbv
             fa.free(); fb.free()
-        assert len(ran) >= (4 if name == "weighted_3d27" else 7)
+        assert len(ran) >= (4 if name == "weighted_3d27" else 8)
         st.set("tblock", 1)
         fa, fb = nb.Field.from_numpy(ctx, u), nb.Field.from_numpy(ctx, u)
         n0 = ctx.launch_count()
@@ -338,7 +386,7 @@ def test_temporal_blocking_bit_exact(nb, ctx, name, shape, ty, steps):
 def test_temporal_blocking_falls_back_to_single_sweeps(nb, ctx):
     """Bodies/geometries the fused kernel does not take (extra inputs, 2-D, bounds touching the box)
     run step by step with the same result — still on the GPU, never on the CPU."""
-    for name, shape in [("jacobi_star", (20, 24, 32)), ("heat_star", (48, 64))]:
+    for name, shape in [("varcoef_3d7", (20, 24, 32)), ("heat_star", (48, 64))]:
         text, n_extra = H.program(name, list(shape))
         u, extra = H.inputs(shape, n_extra, "f64", seed=8)
         want = H.oracle_steps(text, u, extra, 6)
@@ -352,6 +400,40 @@ def test_temporal_blocking_falls_back_to_single_sweeps(nb, ctx):
         assert H.bits_equal(r.download(), want)
         for f in [fa, fb] + fx:
             f.free()
+        m.destroy()
+
+
+@pytest.mark.parametrize("shape,ty,steps", [
+    ((40, 48, 64), "f64", 8),
+    ((21, 37, 70), "f64", 7),        # ragged extents, odd step count
+    ((150, 20, 136), "f64", 4),      # several z chunks
+    ((24, 40, 72), "f32", 10),
+])
+def test_temporal_blocking_with_a_pointwise_input(nb, ctx, shape, ty, steps):
+    """Jacobi with a right-hand side (BASELINE configs[4]: "temporal blocking"): u and f are two inputs,
+    f is read at offset 0 only, and a fused pair of steps is apply(apply(u, f), f).  The z-marching
+    kernel streams f from global memory at both levels; the result equals the step-by-step oracle bitwise."""
+    text, n_extra = H.program("jacobi_star", list(shape), ty)
+    assert n_extra == 1
+    u, extra = H.inputs(shape, n_extra, ty, seed=43)
+    want = H.oracle_steps(text, u, extra, steps)
+    m = nb.Module(text)
+    try:
+        st = m.stencil(ctx, 0)
+        for tbv in ["auto", "tb2m:64x24", "tb2m:128x10", "tb2m:128x14"]:
+            if tbv != "auto":
+                st.set("variant", tbv)
+            fa, fb = nb.Field.from_numpy(ctx, u), nb.Field.from_numpy(ctx, u)
+            fx = [nb.Field.from_numpy(ctx, e) for e in extra]
+            n0 = ctx.launch_count()
+            r = st.run_steps(fa, fb, fx, steps)
+            assert ctx.launch_count() - n0 == steps // 2 + steps % 2
+            assert H.bits_equal(r.download(), want), "%s differs on %s after %d steps" % (tbv, shape, steps)
+            if steps % 2 == 0 and tbv != "auto":
+                assert st.variant() == tbv
+            for f in [fa, fb] + fx:
+                f.free()
+    finally:
         m.destroy()
 
 
