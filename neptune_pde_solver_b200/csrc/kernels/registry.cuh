@@ -232,6 +232,7 @@ typedef Tb2Cfg<64, 32, 4, 5, 1> Tb2D;
 typedef Tb2Cfg<128, 14, 2, 6, 1> Tb2mA;
 typedef Tb2Cfg<64, 16, 2, 6, 2> Tb2mB;
 typedef Tb2Cfg<128, 14, 2, 8, 1> Tb2mC;
+typedef Tb2Cfg<128, 14, 2, 6, 1, true> Tb2mAf;
 // 512 threads = 4 warps per SM sub-partition -> up to 128 registers (5 warps per sub-partition: 96)
 typedef Tb2Cfg<64, 24, 2, 8, 1> Tb2mD;
 typedef Tb2Cfg<128, 10, 2, 6, 1> Tb2mE;
@@ -279,6 +280,7 @@ template <class F> struct BodyRegistrar {
             e.variants.push_back(tb2_variant<F, Tb2mB, false, true>("tb2m:64x16"));
             e.variants.push_back(tb2_variant<F, Tb2mC, false, true>("tb2m:128x14n8"));
             e.variants.push_back(tb2_variant<F, Tb2mD, false, true>("tb2m:64x24"));
+            e.variants.push_back(tb2_variant<F, Tb2mAf, false, true>("tb2m:128x14f"));
           }
         } else if constexpr (F::NIN == 2 && F::RZ == 1 && F::ZSTAR) {
           // input 0 plus pointwise inputs (Jacobi with a right-hand side): the z-marching form only

@@ -758,7 +758,9 @@ int do_apply(neptune_rt_stencil *s, int n_in, neptune_rt_field *const *in, neptu
     // tb2:128x16 409, tb2:64x16 382 Gupd/s); narrow boxes keep the 64-wide tile so that fewer CTAs idle on a partial column
     if (s->want_tb == "auto") {
       const bool wide = out->ext[2] >= 256;
-      const char *prefer[] = {n_in > 1 ? "tb2m:64x24" : wide ? "tb2m:128x14" : "tb2:64x16", wide ? "tb2:128x16" : "tb2:64x16"};
+      // two inputs (Jacobi + rhs, r01 768^3): f64 tb2m:64x24 383 / 128x10 340 / 128x14 323 Gupd/s; f32 128x14 536 / 64x24 464
+      const char *two_in = d.dtype == NEPTUNE_RT_F64 ? "tb2m:64x24" : "tb2m:128x14";
+      const char *prefer[] = {n_in > 1 ? two_in : wide ? "tb2m:128x14" : "tb2:64x16", wide ? "tb2:128x16" : "tb2:64x16"};
       for (const char *name : prefer) {
         for (auto &v : s->body->variants)
           if (v.kind == neptune::VARIANT_TB2 && v.fma == s->fma && v.name == name) { pick = &v; break; }
