@@ -232,16 +232,19 @@ typedef Tb2Cfg<64, 32, 4, 5, 1> Tb2D;
 typedef Tb2Cfg<128, 14, 2, 6, 1> Tb2mA;
 typedef Tb2Cfg<64, 16, 2, 6, 2> Tb2mB;
 typedef Tb2Cfg<128, 14, 2, 8, 1> Tb2mC;
-typedef Tb2Cfg<128, 14, 2, 6, 1, true> Tb2mAf;
 // 512 threads = 4 warps per SM sub-partition -> up to 128 registers (5 warps per sub-partition: 96)
 typedef Tb2Cfg<64, 24, 2, 8, 1> Tb2mD;
 typedef Tb2Cfg<128, 10, 2, 6, 1> Tb2mE;
 typedef Tb2Cfg<64, 24, 2, 5, 1> Tb2mG;
 typedef Tb2Cfg<128, 14, 2, 4, 1> Tb2mF;   // two staged tiles per slot: four slots fit beside the level-1 planes
 typedef TileCfg<64, 8, 1, 6, 1> Tile3W;   // many-input bodies (one coefficient field per tap)
-typedef RowCfg<512, 4, 4, 3> Rows512;     // strip of 512 columns (elements = TX), 4 rows per stage, ring of 4
-typedef RowCfg<256, 8, 4, 4> Rows256;
-typedef RowCfg<1024, 2, 6, 1> Rows1024;
+typedef TileCfg<64, 7, 1, 6, 2> Tile3W2;  // 256 threads, two CTAs per SM at 128 registers
+typedef TileCfg<64, 14, 1, 5, 1> Tile3W3; // 480 threads, one CTA per SM at 128 registers
+// strip of TX columns, RB rows per stage (a multiple of the 3-row window, so the unrolled stage loop needs
+// no register moves), ring of NS stages, CTAs per SM
+typedef RowCfg<512, 3, 5, 3> Rows512;
+typedef RowCfg<256, 6, 4, 4> Rows256;
+typedef RowCfg<1024, 3, 4, 1> Rows1024;
 typedef TileCfg<128, 32, 8, 3, 2> Tile2A;
 typedef TileCfg<128, 16, 4, 4, 2> Tile2B;
 typedef TileCfg<64, 64, 8, 3, 2> Tile2C;
@@ -263,6 +266,10 @@ template <class F> struct BodyRegistrar {
       if constexpr (F::NIN > 4) {
         e.variants.push_back(tma_variant<F, Tile3W, false>("tma:64x8"));
         e.variants.push_back(tma_variant<F, Tile3W, true>("tma:64x8"));
+        if constexpr (F::RZ > 0) {
+          e.variants.push_back(tma_variant<F, Tile3W2, false>("tma:64x7"));
+          e.variants.push_back(tma_variant<F, Tile3W3, false>("tma:64x14"));
+        }
       } else if constexpr (F::RZ > 0) {
         e.variants.push_back(tma_variant<F, Tile3A, false>("tma:64x16"));
         e.variants.push_back(tma_variant<F, Tile3A, true>("tma:64x16"));
@@ -280,7 +287,6 @@ template <class F> struct BodyRegistrar {
             e.variants.push_back(tb2_variant<F, Tb2mB, false, true>("tb2m:64x16"));
             e.variants.push_back(tb2_variant<F, Tb2mC, false, true>("tb2m:128x14n8"));
             e.variants.push_back(tb2_variant<F, Tb2mD, false, true>("tb2m:64x24"));
-            e.variants.push_back(tb2_variant<F, Tb2mAf, false, true>("tb2m:128x14f"));
           }
         } else if constexpr (F::NIN == 2 && F::RZ == 1 && F::ZSTAR) {
           // input 0 plus pointwise inputs (Jacobi with a right-hand side): the z-marching form only

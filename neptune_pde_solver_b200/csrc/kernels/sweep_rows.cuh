@@ -74,6 +74,7 @@ sweep_rows(const __grid_constant__ KParams<F> p) {
   constexpr int VX = G::VX, HX = G::HX, NS = G::NS, RB = G::RB, S = G::S;
   constexpr int NPW = F::NIN > 1 ? F::NIN - 1 : 1;
   constexpr int NCW = G::CONSUMERS / 32;
+  constexpr unsigned XFULL = (1u << VX) - 1u;
 
   extern __shared__ __align__(128) unsigned char smem_raw[];
   unsigned char *smem = smem_raw + ((128u - (smem_u32(smem_raw) & 127u)) & 127u);
@@ -98,9 +99,11 @@ sweep_rows(const __grid_constant__ KParams<F> p) {
     ye = min(p.whi[1], yb + p.zchunk);
     x0 = (p.cxo + cx) * C::TX;
   };
+  // Stage sequence of an item: a head stage with input rows yb-1 and yb (they fill the window, no
+  // output), then stages of RB input rows yb+1+m*RB .. ; input row yb+1+q completes output row yb+q.
 
   if (tid >= G::CONSUMERS) {
-    // ---- producer: input rows yb-1 .. ye of every item, RB rows per stage -------------------------
+    // ---- producer -----------------------------------------------------------------------------------
     if (tid == G::CONSUMERS) {
       const T *src0 = p.in[F::STAGED];
       const long long sy = p.in_sy[F::STAGED];
@@ -108,18 +111,16 @@ sweep_rows(const __grid_constant__ KParams<F> p) {
       for (int item = blockIdx.x; item < p.nitems; item += gridDim.x) {
         int yb, ye, x0;
         geom(item, yb, ye, x0);
-        const int rows = ye - yb + 2;
         const int xs = max(0, x0 - HX), xe = min(p.nx, x0 + C::TX + HX);
         const uint32_t row_bytes = (uint32_t)(xe - xs) * S;
         const uint32_t doff = (uint32_t)(xs - (x0 - HX)) * S;
-        for (int t0 = 0; t0 < rows; t0 += RB, ++n) {
+        // ya = first input row of the stage, cnt = rows it holds
+        for (int ya = yb - 1, cnt = 2; ya <= ye; ya += cnt, cnt = min(RB, ye + 1 - ya), ++n) {
           const unsigned s = n % NS;
           mbar_wait(empty0 + 8 * s, ((n / NS) & 1) ^ 1);
-          // rows of this stage that exist in the box (the first / last row of the box's edge chunks do not)
-          const int ya = yb - 1 + t0;
-          const int r_lo = max(0, -ya), r_hi = min(min(RB, rows - t0), p.ny - ya);
-          const int nvalid = max(0, r_hi - r_lo);
-          mbar_expect_tx(full0 + 8 * s, (uint32_t)nvalid * row_bytes);
+          // rows that exist in the box (row -1 and row ny of the box's edge chunks do not)
+          const int r_lo = max(0, -ya), r_hi = min(cnt, p.ny - ya);
+          mbar_expect_tx(full0 + 8 * s, (uint32_t)max(0, r_hi - r_lo) * row_bytes);
           for (int r = r_lo; r < r_hi; ++r)
             bulk_load_1d(stage0 + s * G::STAGE_BYTES + r * G::ROW_BYTES + doff, src0 + (long long)(ya + r) * sy + xs, row_bytes,
                          full0 + 8 * s);
@@ -134,6 +135,27 @@ sweep_rows(const __grid_constant__ KParams<F> p) {
   const bool lane0 = (tid & 31) == 0;
   const bool swap = ((tid >> 3) & 1) != 0;   // alternate left/right halo reads between lane groups (bank conflicts)
   unsigned n = 0;
+  T w[3][VX + 2];   // rows y-1, y, y+1 of input 0 around the thread's VX columns
+#pragma unroll
+  for (int a = 0; a < 3; ++a)
+#pragma unroll
+    for (int b = 0; b < VX + 2; ++b) w[a][b] = T(0);
+
+  // shift the window down and read one staged row into w[2]
+  auto push_row = [&](const T *row) {
+#pragma unroll
+    for (int b = 0; b < VX + 2; ++b) { w[0][b] = w[1][b]; w[1][b] = w[2][b]; }
+    T ctr[VX];
+    lds_vec<T, VX>(ctr, row);
+#pragma unroll
+    for (int i = 0; i < VX; ++i) w[2][1 + i] = ctr[i];
+    if constexpr (G::RX > 0) {
+      const T v1 = row[swap ? VX : -1], v2 = row[swap ? -1 : VX];
+      w[2][0] = swap ? v2 : v1;
+      w[2][VX + 1] = swap ? v1 : v2;
+    }
+  };
+
   for (int item = blockIdx.x; item < p.nitems; item += gridDim.x) {
     int yb, ye, x0;
     geom(item, yb, ye, x0);
@@ -144,27 +166,60 @@ sweep_rows(const __grid_constant__ KParams<F> p) {
 #pragma unroll
     for (int ix = 0; ix < VX; ++ix)
       if (gx + ix >= p.blo[2] && gx + ix < p.bhi[2]) xmask |= 1u << ix;
-    const int rows = ye - yb + 2;
-    T w[3][VX + 2];
-#pragma unroll
-    for (int a = 0; a < 3; ++a)
-#pragma unroll
-      for (int b = 0; b < VX + 2; ++b) w[a][b] = T(0);
+    const bool xfast = live && full_vec && xmask == XFULL;
     T *dst = p.out + (long long)yb * p.out_sy + gx;
 
-    for (int t0 = 0; t0 < rows; t0 += RB, ++n) {
+    // head stage: rows yb-1, yb
+    {
       const unsigned s = n % NS;
       mbar_wait(full0 + 8 * s, (n / NS) & 1);
+      if (live) {
+        const T *sp = reinterpret_cast<const T *>(smem + s * G::STAGE_BYTES) + HX + lx;
+        push_row(sp);
+        push_row(sp + G::SXP);
+      }
+      __syncwarp();
+      if (lane0) mbar_arrive(empty0 + 8 * s);
+      ++n;
+    }
+
+    for (int y0 = yb; y0 < ye; y0 += RB, ++n) {   // this stage completes output rows y0 .. y0+cnt-1
+      const unsigned s = n % NS;
+      const int cnt = min(RB, ye - y0);
+      mbar_wait(full0 + 8 * s, (n / NS) & 1);
       const T *sp = reinterpret_cast<const T *>(smem + s * G::STAGE_BYTES) + HX + lx;
+      if (xfast && cnt == RB && y0 >= p.blo[1] && y0 + RB <= p.bhi[1]) {
+        // steady state: a whole stage strictly inside the apply bounds — no row, bounds or edge tests
+        T pw[RB][NPW][VX];
+        if constexpr (F::NIN > 1) {
 #pragma unroll
-      for (int r = 0; r < RB; ++r) {
-        const int t = t0 + r;
-        if (t < rows) {
-          const int y = yb + t - 2;   // output row completed by this input row
-          // pointwise inputs of the output row
+          for (int r = 0; r < RB; ++r)
+            static_for<F::NIN>([&](auto kc) {
+              constexpr int K = decltype(kc)::value;
+              if constexpr (K != F::STAGED)
+                ldg_vec<T, VX>(pw[r][K < F::STAGED ? K : K - 1], p.in[K] + (long long)(y0 + r) * p.in_sy[K] + gx);
+            });
+        }
+#pragma unroll
+        for (int r = 0; r < RB; ++r) {
+          push_row(sp + r * G::SXP);
+          T res[VX];
+          static_for<VX>([&](auto ixc) {
+            constexpr int IX = decltype(ixc)::value;
+            RowAcc<F, VX, IX> acc{w, pw[r]};
+            res[IX] = F::template eval<FMA>(acc, p.c);
+          });
+          stg_vec<T, VX, false>(dst + r * p.out_sy, res);
+        }
+      } else if (live) {
+        // edges: ragged last stage, rows or columns outside the apply bounds (copy-through), partial vectors
+        for (int r = 0; r < cnt; ++r) {
+          const int y = y0 + r;
+          push_row(sp + r * G::SXP);
+          const bool yin = y >= p.blo[1] && y < p.bhi[1];
           T pw[NPW][VX];
           if constexpr (F::NIN > 1) {
-            if (live && t >= 2 && xmask && y >= p.blo[1] && y < p.bhi[1]) {
+            if (yin && xmask) {
               static_for<F::NIN>([&](auto kc) {
                 constexpr int K = decltype(kc)::value;
                 if constexpr (K != F::STAGED)
@@ -172,51 +227,30 @@ sweep_rows(const __grid_constant__ KParams<F> p) {
               });
             }
           }
-          // shift the window down one row and read the new row
-#pragma unroll
-          for (int b = 0; b < VX + 2; ++b) { w[0][b] = w[1][b]; w[1][b] = w[2][b]; }
-          if (live) {
-            const T *row = sp + r * G::SXP;
-            T ctr[VX];
-            lds_vec<T, VX>(ctr, row);
-#pragma unroll
-            for (int i = 0; i < VX; ++i) w[2][1 + i] = ctr[i];
-            if constexpr (G::RX > 0) {
-              const T v1 = row[swap ? VX : -1], v2 = row[swap ? -1 : VX];
-              w[2][0] = swap ? v2 : v1;
-              w[2][VX + 1] = swap ? v1 : v2;
+          T res[VX];
+          static_for<VX>([&](auto ixc) {
+            constexpr int IX = decltype(ixc)::value;
+            T v = w[1][IX + 1];   // copy-through: input 0 at this point
+            if (yin && ((xmask >> IX) & 1u)) {
+              RowAcc<F, VX, IX> acc{w, pw};
+              v = F::template eval<FMA>(acc, p.c);
             }
-          }
-          if (r == RB - 1 || t == rows - 1) {
-            // every row of this stage is in registers as far as this warp needs it
-            __syncwarp();
-            if (lane0) mbar_arrive(empty0 + 8 * s);
-          }
-          if (t >= 2) {
-            if (live) {
-              const bool yin = y >= p.blo[1] && y < p.bhi[1];
-              T res[VX];
-              static_for<VX>([&](auto ixc) {
-                constexpr int IX = decltype(ixc)::value;
-                T v = w[1][IX + 1];   // copy-through: input 0 at this point
-                if (yin && ((xmask >> IX) & 1u)) {
-                  RowAcc<F, VX, IX> acc{w, pw};
-                  v = F::template eval<FMA>(acc, p.c);
-                }
-                res[IX] = v;
-              });
-              if (full_vec) {
-                stg_vec<T, VX, false>(dst, res);
-              } else {
+            res[IX] = v;
+          });
+          T *d = dst + r * p.out_sy;
+          if (full_vec) {
+            stg_vec<T, VX, false>(d, res);
+          } else {
 #pragma unroll
-                for (int ix = 0; ix < VX; ++ix)
-                  if (gx + ix >= p.wlo[2] && gx + ix < p.whi[2]) dst[ix] = res[ix];
-              }
-            }
-            dst += p.out_sy;
+            for (int ix = 0; ix < VX; ++ix)
+              if (gx + ix >= p.wlo[2] && gx + ix < p.whi[2]) d[ix] = res[ix];
           }
         }
       }
+      // every row of this stage is in registers as far as this warp needs it
+      __syncwarp();
+      if (lane0) mbar_arrive(empty0 + 8 * s);
+      dst += (long long)RB * p.out_sy;
     }
   }
 }

@@ -24,9 +24,8 @@
 
 namespace neptune {
 
-template <int TX_, int TY_, int VY_, int NS_, int MINB_, bool FIXUP_ = false> struct Tb2Cfg {
+template <int TX_, int TY_, int VY_, int NS_, int MINB_> struct Tb2Cfg {
   static constexpr int TX = TX_, TY = TY_, VY = VY_, NS = NS_, MINB = MINB_;
-  static constexpr bool FIXUP = FIXUP_;   // sweep_tb2m: evaluate every point, select copy-through values only at the bounds' edge
 };
 
 template <class F, class C> struct Tb2Geom {

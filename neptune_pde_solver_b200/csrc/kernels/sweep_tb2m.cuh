@@ -113,7 +113,6 @@ sweep_tb2m(const __grid_constant__ KParams<F> p, const __grid_constant__ CUtenso
   constexpr int VX = G::VX, VY = G::VY, NS = G::NS;
   constexpr int NCW = G::CONSUMERS / 32;
   constexpr int NPW = F::NIN > 1 ? F::NIN - 1 : 1;
-  constexpr unsigned FULLMASK = (VY * VX >= 32) ? 0xffffffffu : ((1u << (VY * VX)) - 1u);
 
   extern __shared__ __align__(128) unsigned char smem_raw[];
   unsigned char *smem = smem_raw + ((128u - (smem_u32(smem_raw) & 127u)) & 127u);
@@ -170,7 +169,8 @@ sweep_tb2m(const __grid_constant__ KParams<F> p, const __grid_constant__ CUtenso
   // dropped: a 3x unrolled plane loop with statically indexed planes instead of the register moves
   // below (ptxas spilled, 245 Gupd/s); an `all in bounds` fast path without the copy-through selects
   // (the extra branches keep ptxas from interleaving the DP chains of phases A and B, 293 Gupd/s);
-  // explicit 32-bit shared addresses (390 Gupd/s).  The dependent DADD chain of the body is what the
+  // explicit 32-bit shared addresses (390 Gupd/s); unconditional evaluation with the copy-through selects moved
+  // into a branch taken only at the bounds' edge (402 Gupd/s: same story, the branch splits the stream).  The dependent DADD chain of the body is what the
   // warps wait on, so instruction-level parallelism across the two phases matters more than count.)
   const bool active = tid < G::ACTIVE;
   const int bx = active ? tid % G::NBX : 0, by = active ? tid / G::NBX : 0;
@@ -262,27 +262,6 @@ sweep_tb2m(const __grid_constant__ KParams<F> p, const __grid_constant__ CUtenso
             for (int ix = 0; ix < VX; ++ix) wa[1 + iy][1 + ix] = ac[iy][ix];
           const unsigned m = (k - 1 >= p.blo[0] && k - 1 < p.bhi[0]) ? bmask : 0u;
           T *l1p = ring1 + (c1 & 1u) * L1_ELEMS + soff1;
-          if constexpr (C::FIXUP) {
-            // every point evaluated unconditionally in one straight-line stream; the copy-through
-            // selects run only in threads whose block touches the edge of the apply bounds
-            static_for<VY>([&](auto iyc) {
-              constexpr int IY = decltype(iyc)::value;
-              static_for<VX>([&](auto ixc) {
-                constexpr int IX = decltype(ixc)::value;
-                MarchAcc<F, VY, VX, IY, IX> acc{am, wa, ap, qc};
-                ra[IY][IX] = F::template eval<FMA>(acc, p.c);
-              });
-            });
-            if (m != FULLMASK) {
-#pragma unroll
-              for (int iy = 0; iy < VY; ++iy)
-#pragma unroll
-                for (int ix = 0; ix < VX; ++ix)
-                  if (!((m >> (iy * VX + ix)) & 1u)) ra[iy][ix] = ac[iy][ix];
-            }
-#pragma unroll
-            for (int iy = 0; iy < VY; ++iy) stg_vec<T, VX, false>(l1p + iy * G::P1, ra[iy]);
-          } else {
           static_for<VY>([&](auto iyc) {
             constexpr int IY = decltype(iyc)::value;
             static_for<VX>([&](auto ixc) {
@@ -293,7 +272,6 @@ sweep_tb2m(const __grid_constant__ KParams<F> p, const __grid_constant__ CUtenso
             });
             stg_vec<T, VX, false>(l1p + IY * G::P1, ra[IY]);  // shared-memory store of the level-1 block
           });
-          }
         }
         // ---- phase B: level-2 plane k-2 from level-1 planes k-3 (bm), k-2 (bc + halo), k-1 (ra) --
         if (j >= 4 && wmask != 0) {
@@ -304,36 +282,14 @@ sweep_tb2m(const __grid_constant__ KParams<F> p, const __grid_constant__ CUtenso
 #pragma unroll
             for (int ix = 0; ix < VX; ++ix) wb[1 + iy][1 + ix] = bc[iy][ix];
           const unsigned m = (k - 2 >= p.blo[0] && k - 2 < p.bhi[0]) ? bmask : 0u;
-          T rb[VY][VX];
-          if constexpr (C::FIXUP) {
-            static_for<VY>([&](auto iyc) {
-              constexpr int IY = decltype(iyc)::value;
-              static_for<VX>([&](auto ixc) {
-                constexpr int IX = decltype(ixc)::value;
-                MarchAcc<F, VY, VX, IY, IX> acc{bm, wb, ra, qm};
-                rb[IY][IX] = F::template eval<FMA>(acc, p.c);
-              });
-            });
-            if (m != FULLMASK) {
-#pragma unroll
-              for (int iy = 0; iy < VY; ++iy)
-#pragma unroll
-                for (int ix = 0; ix < VX; ++ix)
-                  if (!((m >> (iy * VX + ix)) & 1u)) rb[iy][ix] = bc[iy][ix];
-            }
-          }
           static_for<VY>([&](auto iyc) {
             constexpr int IY = decltype(iyc)::value;
             T res[VX];
             static_for<VX>([&](auto ixc) {
               constexpr int IX = decltype(ixc)::value;
-              if constexpr (C::FIXUP) {
-                res[IX] = rb[IY][IX];
-              } else {
-                MarchAcc<F, VY, VX, IY, IX> acc{bm, wb, ra, qm};
-                const T v = F::template eval<FMA>(acc, p.c);
-                res[IX] = ((m >> (IY * VX + IX)) & 1u) ? v : bc[IY][IX];
-              }
+              MarchAcc<F, VY, VX, IY, IX> acc{bm, wb, ra, qm};
+              const T v = F::template eval<FMA>(acc, p.c);
+              res[IX] = ((m >> (IY * VX + IX)) & 1u) ? v : bc[IY][IX];
             });
             constexpr unsigned ROW = ((1u << VX) - 1u) << (IY * VX);
             T *d = dst + IY * p.out_sy;

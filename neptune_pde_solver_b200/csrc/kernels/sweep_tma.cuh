@@ -131,6 +131,22 @@ template <class F, class G, int VY, int IY, int IX> struct WinAcc {
   }
 };
 
+// the same with the pointwise inputs of one thread-tile row only (many-input bodies load them row by row)
+template <class F, class G, int VY, int IY, int IX> struct WinAccRow {
+  typedef typename F::T T;
+  static constexpr int NPW = F::NIN > 1 ? F::NIN - 1 : 1;
+  const T (&w)[2 * G::RZ + 1][VY + 2 * G::RY][G::VX + 2 * G::RX];
+  const T (&pw)[NPW][G::VX];
+  template <int K, int DZ, int DY, int DX> __device__ __forceinline__ T tap() const {
+    if constexpr (K == F::STAGED) {
+      return w[DZ + G::RZ][IY + DY + G::RY][IX + DX + G::RX];
+    } else {
+      static_assert(DZ == 0 && DY == 0 && DX == 0, "non-staged inputs are read at offset 0 only");
+      return pw[K < F::STAGED ? K : K - 1][IX];
+    }
+  }
+};
+
 template <class F, class C, bool FMA>
 __global__ void __launch_bounds__((TmaGeom<F, C>::THREADS), C::MINB)
 sweep_tma(const __grid_constant__ KParams<F> p, const __grid_constant__ CUtensorMap tmap) {
@@ -139,6 +155,7 @@ sweep_tma(const __grid_constant__ KParams<F> p, const __grid_constant__ CUtensor
   constexpr int RZ = G::RZ, RY = G::RY, RX = G::RX, HX = G::HX, VX = G::VX, VY = C::VY, NS = G::NS;
   constexpr int NPW = F::NIN > 1 ? F::NIN - 1 : 1;
   constexpr int NCW = G::CONSUMERS / 32;  // consumer warps
+  constexpr bool LATE_PW = F::NIN > 4;
 
   extern __shared__ __align__(128) unsigned char smem_raw[];
   unsigned char *smem = reinterpret_cast<unsigned char *>((reinterpret_cast<uintptr_t>(smem_raw) + 127) & ~uintptr_t(127));
@@ -203,9 +220,13 @@ sweep_tma(const __grid_constant__ KParams<F> p, const __grid_constant__ CUtensor
       const bool compute = j >= 2 * RZ;
       const int z = zb + j - 2 * RZ;
 
-      // pointwise inputs: 128-bit streaming loads, issued before the wait so they overlap it
+      // pointwise inputs: 128-bit streaming loads.  Few inputs: issued before the wait so they overlap it.
+      // Many inputs (one coefficient field per tap): issued right before the body instead, in the same
+      // basic block, so that ptxas can interleave loads and arithmetic within the register budget of two
+      // CTAs per SM (r01 ncu of the 27-field body: all 27 vectors preloaded = 168 registers, one CTA of 9
+      // warps per SM, DRAM at 4.4 TB/s waiting on `long_scoreboard`).
       T pw[NPW][VY][VX];
-      if constexpr (F::NIN > 1) {
+      auto load_pw = [&]() {
         if (compute && live) {
           static_for<F::NIN>([&](auto kc) {
             constexpr int K = decltype(kc)::value;
@@ -226,7 +247,8 @@ sweep_tma(const __grid_constant__ KParams<F> p, const __grid_constant__ CUtensor
             }
           });
         }
-      }
+      };
+      if constexpr (F::NIN > 1 && !LATE_PW) load_pw();
 
       mbar_wait(full0 + 8 * (n % NS), (n / NS) & 1);
       if (!compute) continue;
@@ -264,6 +286,59 @@ sweep_tma(const __grid_constant__ KParams<F> p, const __grid_constant__ CUtensor
         }
       }
 
+      if constexpr (LATE_PW) {
+        if (live) {
+          const bool zin = z >= p.blo[0] && z < p.bhi[0];
+          const bool xin = gx >= p.blo[2] && gx + VX <= p.bhi[2] && gx >= p.wlo[2] && gx + VX <= p.whi[2];
+          static_for<VY>([&](auto iyc) {
+            constexpr int IY = decltype(iyc)::value;
+            const int y = gy + IY;
+            if (y < p.whi[1] && y >= p.wlo[1]) {
+              T *dst = p.out + (long long)z * p.out_sz + (long long)y * p.out_sy + gx;
+              if (zin && xin && y >= p.blo[1] && y < p.bhi[1]) {
+                // whole vector inside the apply bounds (which lie inside every input's box): unconditional
+                // vector loads and the body in ONE basic block
+                T pr[NPW][VX];
+                static_for<F::NIN>([&](auto kc) {
+                  constexpr int K = decltype(kc)::value;
+                  if constexpr (K != F::STAGED)
+                    ldg_vec<T, VX>(pr[K < F::STAGED ? K : K - 1],
+                                   p.in[K] + (long long)z * p.in_sz[K] + (long long)y * p.in_sy[K] + gx);
+                });
+                T res[VX];
+                static_for<VX>([&](auto ixc) {
+                  constexpr int IX = decltype(ixc)::value;
+                  WinAccRow<F, G, VY, IY, IX> acc{w, pr};
+                  res[IX] = F::template eval<FMA>(acc, p.c);
+                });
+                stg_vec<T, VX, C::STREAM>(dst, res);
+              } else {
+                // edge of the bounds or of the written box: point by point
+                static_for<VX>([&](auto ixc) {
+                  constexpr int IX = decltype(ixc)::value;
+                  const int x = gx + IX;
+                  if (x >= p.wlo[2] && x < p.whi[2]) {
+                    T v = w[RZ][IY + RY][IX + RX];
+                    if (zin && y >= p.blo[1] && y < p.bhi[1] && x >= p.blo[2] && x < p.bhi[2]) {
+                      T pr[NPW][VX];
+                      static_for<F::NIN>([&](auto kc) {
+                        constexpr int K = decltype(kc)::value;
+                        if constexpr (K != F::STAGED)
+                          pr[K < F::STAGED ? K : K - 1][IX] =
+                              __ldg(p.in[K] + (long long)z * p.in_sz[K] + (long long)y * p.in_sy[K] + x);
+                      });
+                      WinAccRow<F, G, VY, IY, IX> acc{w, pr};
+                      v = F::template eval<FMA>(acc, p.c);
+                    }
+                    dst[IX] = v;
+                  }
+                });
+              }
+            }
+          });
+        }
+        continue;
+      }
       if (live) {
         const bool zin = z >= p.blo[0] && z < p.bhi[0];
         static_for<VY>([&](auto iyc) {
