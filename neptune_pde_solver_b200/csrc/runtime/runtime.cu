@@ -774,10 +774,10 @@ int do_apply(neptune_rt_stencil *s, int n_in, neptune_rt_field *const *in, neptu
       for (auto &v : s->body->variants)
         if (v.kind == neptune::VARIANT_TB2 && (s->want_tb == "auto" || v.name == s->want_tb)) { pick = &v; break; }
   } else if (s->want == "auto") {
-    // rank 2: the row-marching kernel (sweep_rows.cuh); narrow boxes take the narrower strip so that the
-    // persistent grid has enough (row chunk, strip) items to balance
+    // rank 2: the row-marching kernel (sweep_rows.cuh); narrow boxes take the narrower strip
     if (tma_ok) {
-      const char *name = out->ext[2] >= 8192 ? "rows:512" : "rows:256";
+      // r01: 16384^2 9-pt rows:1024 360 / rows:512 351 / rows:256 344 Gupd/s; 4096^2 5-pt 322 / 314 / 289
+      const char *name = out->ext[2] >= 2048 ? "rows:1024" : out->ext[2] >= 1024 ? "rows:512" : "rows:256";
       for (auto &v : s->body->variants)
         if (v.kind == neptune::VARIANT_ROWS && v.fma == s->fma && v.name == name) { pick = &v; break; }
       if (!pick)
