@@ -249,7 +249,7 @@ def run_b200(args):
     if world > 1:
         # two ghost planes per neighbour side where the body has a temporally blocked kernel: one
         # exchange of two planes per fused pair of steps (neptune_rt_stencil_set_slab)
-        slab = Slab(gdesc, world, rank, halo=2 * gdesc.radius0() if kind in ("heat_star", "jacobi_star") and len(gshape) == 3 and args.tblock != 1 else None)
+        slab = Slab(gdesc, world, rank, halo=2 * gdesc.radius0() if kind in ("heat_star", "jacobi_star", "heat_box_2d9") and args.tblock != 1 else None)
         lshape = list(slab.local_shape(gshape))
         from neptune_pde_solver_b200 import mlir_builders as mb  # local program: same body, local bounds
         ldesc = slab.local

@@ -9,6 +9,7 @@
 #include "sweep_tb2.cuh"
 #include "sweep_tb2m.cuh"
 #include "sweep_rows.cuh"
+#include "sweep_rows2.cuh"
 
 namespace neptune {
 
@@ -190,6 +191,56 @@ template <class F, class C, bool FMA> Variant rows_variant(const char *name) {
   return v;
 }
 
+// rank-2 temporally blocked row marching (sweep_rows2.cuh)
+template <class F, class C, bool FMA> int launch_rows2(const SweepArgs &a) {
+  typedef Rows2Geom<F, C> G;
+  auto kernel = sweep_rows2<F, C, FMA>;
+  static int occ_cached[16] = {0};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (dev < 0 || dev >= 16) dev = 0;
+  if (occ_cached[dev] == 0) {
+    cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, G::SMEM_BYTES);
+    if (e != cudaSuccess) return (int)e;
+    int occ = 0;
+    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kernel, G::THREADS, G::SMEM_BYTES);
+    if (e != cudaSuccess) return (int)e;
+    if (occ < 1) return (int)cudaErrorLaunchOutOfResources;
+    occ_cached[dev] = occ;
+  }
+  KParams<F> p;
+  fill_params<F>(p, a);
+  const int wy = a.whi[1] - a.wlo[1];
+  if (wy <= 0 || a.whi[2] <= a.wlo[2]) return 0;
+  p.cxo = a.wlo[2] / G::TX;
+  p.ncx = (a.whi[2] + G::TX - 1) / G::TX - p.cxo;
+  p.ncy = 1;
+  const int slots = a.sm_count * occ_cached[dev];
+  p.zchunk = a.zchunk > 0 ? std::min(a.zchunk, wy) : choose_zchunk(wy, p.ncx, slots, 2);
+  p.nchunks = (wy + p.zchunk - 1) / p.zchunk;
+  const long long items = (long long)p.nchunks * p.ncx;
+  if (items > 0x7fffffffLL) return (int)cudaErrorInvalidConfiguration;
+  p.nitems = (int)items;
+  const int grid = (int)std::min<long long>(items, slots);
+  kernel<<<grid, G::THREADS, G::SMEM_BYTES, a.stream>>>(p);
+  return (int)cudaGetLastError();
+}
+
+template <class F, class C, bool FMA> Variant rows2_variant(const char *name) {
+  typedef Rows2Geom<F, C> G;
+  Variant v;
+  v.name = name;
+  v.kind = VARIANT_TB2;
+  v.needs_tmap = false;
+  v.fma = FMA;
+  v.steps = 2;
+  v.tx = G::TX; v.ty = C::RB;
+  v.halo_x = 2 * G::VX; v.halo_y = 2;
+  v.threads = G::THREADS; v.smem = G::SMEM_BYTES;
+  v.launch = &launch_rows2<F, C, FMA>;
+  return v;
+}
+
 template <class F, class C, bool FMA, bool MARCH = false> Variant tb2_variant(const char *name) {
   typedef typename std::conditional<MARCH, Tb2mGeom<F, C>, Tb2Geom<F, C>>::type G;
   Variant v;
@@ -245,6 +296,9 @@ typedef TileCfg<64, 14, 1, 5, 1> Tile3W3; // 480 threads, one CTA per SM at 128 
 typedef RowCfg<512, 3, 5, 3> Rows512;
 typedef RowCfg<256, 6, 4, 4> Rows256;
 typedef RowCfg<1024, 3, 4, 1> Rows1024;
+typedef Rows2Cfg<256, 3, 5, 2> Rows2A;     // 256 consumer threads (strip of 508 f64 columns), 3 rows per stage, two CTAs per SM
+typedef Rows2Cfg<256, 6, 4, 1> Rows2B;
+typedef Rows2Cfg<512, 3, 4, 1> Rows2C;
 typedef TileCfg<128, 32, 8, 3, 2> Tile2A;
 typedef TileCfg<128, 16, 4, 4, 2> Tile2B;
 typedef TileCfg<64, 64, 8, 3, 2> Tile2C;
@@ -301,6 +355,12 @@ template <class F> struct BodyRegistrar {
           e.variants.push_back(rows_variant<F, Rows512, true>("rows:512"));
           e.variants.push_back(rows_variant<F, Rows256, false>("rows:256"));
           e.variants.push_back(rows_variant<F, Rows1024, false>("rows:1024"));
+          if constexpr (F::NIN == 1) {
+            e.variants.push_back(rows2_variant<F, Rows2A, false>("tb2r:256x3"));
+            e.variants.push_back(rows2_variant<F, Rows2A, true>("tb2r:256x3"));
+            e.variants.push_back(rows2_variant<F, Rows2B, false>("tb2r:256x6"));
+            e.variants.push_back(rows2_variant<F, Rows2C, false>("tb2r:512x3"));
+          }
         }
         e.variants.push_back(tma_variant<F, Tile2A, false>("tma:128x32"));
         e.variants.push_back(tma_variant<F, Tile2A, true>("tma:128x32"));

@@ -42,6 +42,7 @@ struct Variant {
   int halo_x = 0, halo_y = 0;   // box origin = tile origin - halo
   int threads = 0, smem = 0;
   int steps = 1;                // time steps one launch advances (2: temporally blocked)
+  bool needs_tmap = true;       // TMA / TB2 kinds: the launch takes a tensor map of the staged input (row kernels use bulk copies)
   int (*launch)(const SweepArgs &) = nullptr;   // returns a cudaError_t
 };
 

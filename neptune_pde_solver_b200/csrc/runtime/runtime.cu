@@ -664,13 +664,13 @@ bool tb2_eligible(const neptune_rt_stencil *s, neptune_rt_field *a, neptune_rt_f
   const neptune_rt_stencil_desc &d = s->desc.c;
   // inputs beyond input 0 are pointwise (the body registers a tb2 kernel only then) and stay the same
   // fields at both levels: a time loop replaces input 0 only
-  if (!has || d.rank != 3 || d.n_inputs != 1 + n_extra) return false;
+  if (!has || d.rank < 2 || d.n_inputs != 1 + n_extra) return false;   // rank 3: sweep_tb2 / tb2m; rank 2: sweep_rows2
   neptune_rt_field *inN[NEPTUNE_RT_MAX_INPUTS] = {a};
   for (int k = 0; k < n_extra; ++k) inN[k + 1] = extra[k];
   if (!tma_eligible(s, 1 + n_extra, inN, b) || encode_tiled() == nullptr) return false;
-  for (int x = 0; x < 3; ++x)
+  for (int x = 0; x < d.rank; ++x)
     if (d.ub[x] <= d.lb[x]) return false;
-  for (int x = slab ? 1 : 0; x < 3; ++x)
+  for (int x = slab ? 1 : 0; x < d.rank; ++x)
     if (d.lb[x] < d.out_lb[x] + 1 || d.ub[x] > d.out_ub[x] - 1) return false;
   if (slab) {
     const neptune_rt_ctx *c = s->ctx;
@@ -736,11 +736,11 @@ int do_apply(neptune_rt_stencil *s, int n_in, neptune_rt_field *const *in, neptu
     a.wlo[x] = 0;
     a.whi[x] = (int)out->ext[x];
   }
-  if (two_steps && s->slab_set && d.rank == 3) {
+  if (two_steps && s->slab_set) {
     // level-1 planes next to the owned slab lie on ghost planes: test them against the GLOBAL apply
     // bounds (clipped to the local box), not the owned-plane intersection the local descriptor carries
-    a.blo[0] = (int)(std::max(s->slab_glb0, d.out_lb[0]) - d.out_lb[0]);
-    a.bhi[0] = (int)(std::min(s->slab_gub0, d.out_ub[0]) - d.out_lb[0]);
+    a.blo[cd0] = (int)(std::max(s->slab_glb0, d.out_lb[0]) - d.out_lb[0]);
+    a.bhi[cd0] = (int)(std::min(s->slab_gub0, d.out_ub[0]) - d.out_lb[0]);
   }
   a.wlo[cd0] = (int)p0;
   a.whi[cd0] = (int)p1;
@@ -801,7 +801,7 @@ int do_apply(neptune_rt_stencil *s, int n_in, neptune_rt_field *const *in, neptu
   }
   if (!pick) return set_error(c, NEPTUNE_RT_EUNSUPPORTED, "no kernel variant '%s' for this body", s->want.c_str());
   CUtensorMap tm_staged, tm_pw;   // copies: get_tmap's cache may move its entries on the next call
-  if (pick->kind == neptune::VARIANT_TMA || pick->kind == neptune::VARIANT_TB2) {
+  if ((pick->kind == neptune::VARIANT_TMA || pick->kind == neptune::VARIANT_TB2) && pick->needs_tmap) {
     const CUtensorMap *tm = nullptr;
     if (int rc = get_tmap(s, in[s->body->staged]->dptr, in[s->body->staged]->ext, pick->box_x, pick->box_y, &tm)) return rc;
     tm_staged = *tm;

@@ -75,6 +75,7 @@ def _worker(rank, world, port, name, shape, steps, q, halo=None, tblock=0):
     ("heat_star", (64, 48, 64), 5, 2, 1),      # two ghost planes, temporal blocking switched off
     ("weighted_3d27", (48, 24, 32), 6, 2, 0),
     ("heat_star", (48, 20, 256), 6, 2, 0),     # wide box: the z-marching kernel (tb2m) in slab mode
+    ("heat_box_2d9", (96, 1040), 8, 2, 0),     # rank 2, two ghost rows: sweep_rows2 in slab mode
     ("jacobi_star", (64, 40, 72), 8, 2, 0),    # fused pairs with a pointwise right-hand side: f's ghost planes are exchanged once
 ])
 def test_slab_nccl_equals_single_domain(name, shape, steps, halo, tblock):
@@ -95,5 +96,5 @@ def test_slab_nccl_equals_single_domain(name, shape, steps, halo, tblock):
         assert p.exitcode == 0
     ok, used = q.get(timeout=5)
     assert ok is True
-    if halo == 2 and tblock != 1 and name in ("heat_star", "jacobi_star") and steps % 2 == 0:
+    if halo == 2 and tblock != 1 and name in ("heat_star", "jacobi_star", "heat_box_2d9") and steps % 2 == 0:
         assert used.startswith("tb2"), used   # the temporally blocked kernel really ran in slab mode

@@ -383,10 +383,45 @@ def test_temporal_blocking_bit_exact(nb, ctx, name, shape, ty, steps):
         m.destroy()
 
 
+@pytest.mark.parametrize("name,shape,ty,steps", [
+    ("heat_star", (300, 1040), "f64", 8),        # three 508-column strips, several stages
+    ("heat_box_2d9", (70, 2056), "f64", 7),      # corner taps at both levels; odd step count
+    ("heat_box_2d9", (1030, 520), "f32", 6),     # VX = 4: strips of 1016 columns
+    ("weighted_2d9", (64, 512), "f64", 4),
+    ("heat_star", (5, 512), "f64", 4),           # three interior rows: every stage is ragged
+    ("heat_star", (48, 64), "f64", 6),
+])
+def test_temporal_blocking_2d_bit_exact(nb, ctx, name, shape, ty, steps):
+    """sweep_rows2 (rank 2, two steps per launch, level 1 exchanged through shared memory) == the oracle's
+    step-by-step loop, bitwise, for every compiled strip shape and several row-chunk sizes."""
+    text, n_extra = H.program(name, list(shape), ty)
+    assert n_extra == 0
+    u, _ = H.inputs(shape, 0, ty, seed=47)
+    want = H.oracle_steps(text, u, [], steps)
+    m = nb.Module(text)
+    try:
+        st = m.stencil(ctx, 0)
+        for tbv in ["auto", "tb2r:256x3", "tb2r:256x6", "tb2r:512x3"]:
+            for zc in ("0", "16", "7"):
+                if tbv != "auto":
+                    st.set("variant", tbv)
+                st.set("zchunk", zc)
+                fa, fb = nb.Field.from_numpy(ctx, u), nb.Field.from_numpy(ctx, u)
+                n0 = ctx.launch_count()
+                r = st.run_steps(fa, fb, [], steps)
+                assert ctx.launch_count() - n0 == steps // 2 + steps % 2
+                assert H.bits_equal(r.download(), want), "%s zchunk %s differs on %s after %d steps" % (tbv, zc, shape, steps)
+                if steps % 2 == 0:
+                    assert st.variant().startswith("tb2r"), st.variant()
+                fa.free(); fb.free()
+    finally:
+        m.destroy()
+
+
 def test_temporal_blocking_falls_back_to_single_sweeps(nb, ctx):
     """Bodies/geometries the fused kernel does not take (extra inputs, 2-D, bounds touching the box)
     run step by step with the same result — still on the GPU, never on the CPU."""
-    for name, shape in [("varcoef_3d7", (20, 24, 32)), ("heat_star", (48, 64))]:
+    for name, shape in [("varcoef_3d7", (20, 24, 32)), ("jacobi_star", (48, 64))]:
         text, n_extra = H.program(name, list(shape))
         u, extra = H.inputs(shape, n_extra, "f64", seed=8)
         want = H.oracle_steps(text, u, extra, 6)
