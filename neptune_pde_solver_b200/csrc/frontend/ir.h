@@ -5,6 +5,7 @@
 //   ops    wrap/unwrap/load/yield/apply/access/store        NeptuneIROps.td:20-259
 #pragma once
 #include <cstdint>
+#include <functional>
 #include <map>
 #include <memory>
 #include <stdexcept>
@@ -124,6 +125,10 @@ struct BodyInfo {
 BodyInfo analyze_body(const neptune_rt_stencil_desc &d);
 // canonical (z,y,x) offset of a logical offset vector: rank 3 (d0,d1,d2); rank 2 (0,d0,d1); rank 1 (0,0,d0)
 void canonical_offset(int rank, const int64_t *logical, int out_zyx[3]);
+
+// fusion.cpp — fold `%t = A(%x); %y = apply(%x, %t){.. %t[0] ..}` into one apply (bit-identical per point).
+// accept(key): whether a kernel exists for the fused body (NULL: always fuse).  Returns the number of fusions.
+int fuse_applies(Module &m, bool fma, const std::function<bool(uint64_t)> &accept);
 
 // codegen.cpp — CUDA text of the point functor for a body
 std::string functor_name(uint64_t key);

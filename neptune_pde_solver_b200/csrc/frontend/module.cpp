@@ -50,6 +50,7 @@ struct FnInfo {
 struct neptune_b200_module {
   Module mod;
   bool fma = false;
+  int n_fused = 0;   // producer -> consumer apply pairs folded into one sweep (fusion.cpp)
   std::vector<ApplyRec> applies;
   std::map<const Apply *, int> apply_index;
   std::map<std::string, FnInfo> fns;
@@ -105,6 +106,7 @@ void analyze_function(neptune_b200_module &m, const Function &fn, FnInfo &fi) {
   std::set<std::string> touched;  // storage roots already read or written
   std::ostringstream plan;
   plan << fn.name << ":\n";
+  if (m.n_fused) plan << "  (" << m.n_fused << " producer -> consumer apply pair(s) of this module fused into one sweep each)\n";
   for (size_t i = 0; i < fn.ops.size(); ++i) {
     const HostOp &op = fn.ops[i];
     switch (op.kind) {
@@ -406,15 +408,26 @@ extern "C" int neptune_b200_compile(const char *text, const char *pipeline, nept
     return NEPTUNE_RT_EINVAL;
   }
   std::string opts = pl.substr(name.size());
+  bool fuse = true;
   if (!opts.empty()) {
-    if (opts == "{fma=true}" || opts == "{fma=1}") fma = true;
-    else if (opts == "{fma=false}" || opts == "{fma=0}" || opts == "{}") fma = false;
-    else { report("unknown pipeline options '" + opts + "' (supported: {fma=true|false})"); return NEPTUNE_RT_EINVAL; }
+    // {key=value key=value}: fma (allow contraction), fuse (producer -> consumer apply fusion, fusion.cpp)
+    if (opts.size() < 2 || opts.front() != '{' || opts.back() != '}') { report("malformed pipeline options '" + opts + "'"); return NEPTUNE_RT_EINVAL; }
+    std::istringstream is(opts.substr(1, opts.size() - 2));
+    std::string kv;
+    while (is >> kv) {
+      if (!kv.empty() && kv.back() == ',') kv.pop_back();
+      const bool on = kv.size() > 5 && (kv.substr(kv.find('=') + 1) == "true" || kv.substr(kv.find('=') + 1) == "1");
+      const bool off = kv.size() > 5 && (kv.substr(kv.find('=') + 1) == "false" || kv.substr(kv.find('=') + 1) == "0");
+      if (kv.compare(0, 4, "fma=") == 0 && (on || off)) fma = on;
+      else if (kv.compare(0, 5, "fuse=") == 0 && (on || off)) fuse = on;
+      else { report("unknown pipeline option '" + kv + "' (supported: fma=true|false, fuse=true|false)"); return NEPTUNE_RT_EINVAL; }
+    }
   }
   auto *m = new neptune_b200_module();
   m->fma = fma;
   try {
     m->mod = parse_module(text);
+    if (fuse) m->n_fused = fuse_applies(m->mod, fma, [](uint64_t key) { return neptune_rt_body_compiled(key) != 0; });
     for (auto &fn : m->mod.functions)
       for (auto &op : fn.ops)
         if (op.kind == HostOp::ApplyOp) {

@@ -508,6 +508,7 @@ class Parser {
       op.kind = HostOp::ApplyOp;
       if (op.results.size() != 1) fail("neptune_ir.apply must have exactly one result");
       op.apply = std::make_shared<Apply>(parse_apply(op.results[0], name.line));
+      op.operands = op.apply->inputs;   // so that use counts see the apply's inputs
       return op;
     }
     if (n == "arith.constant") {  // host-level scalar (e.g. a dt); never reaches the sweep

@@ -25,7 +25,12 @@ int main(int argc, char **argv) {
     std::stringstream ss;
     ss << in.rdbuf();
     try {
-      neptune::Module m = neptune::parse_module(ss.str());
+      neptune::Module m0 = neptune::parse_module(ss.str());
+      // the bodies as written, then the bodies producer -> consumer fusion makes of them (fusion.cpp)
+      neptune::Module m1 = m0;
+      const int nf = neptune::fuse_applies(m1, false, nullptr);
+      for (int pass = 0; pass < (nf ? 2 : 1); ++pass) {
+      neptune::Module &m = pass ? m1 : m0;
       for (auto &fn : m.functions)
         for (auto &op : fn.ops) {
           if (op.kind != neptune::HostOp::ApplyOp) continue;
@@ -46,6 +51,7 @@ int main(int argc, char **argv) {
           }
           std::printf("%s\n", path.c_str());
         }
+      }
     } catch (const neptune::Diagnostic &e) {
       std::fprintf(stderr, "%s: %s\n", argv[i], e.what());
       rc = 1;

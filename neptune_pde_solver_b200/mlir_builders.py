@@ -316,3 +316,60 @@ def heat_star_then_sum(shape: Sequence[int], alpha: float, ty: str = "f64") -> s
                 "    func.return %%s : %s") % (_bounds(ilb, iub), ty, ty)
     assert tail_old in text
     return text.replace(tail_old, tail_new)
+
+
+def euler_opdef(shape: Sequence[int], dxinv2: float, dt: float, ty: str = "f64") -> str:
+    """Explicit Euler step written the way the reference composes it (`test/smoke_tests/
+    smoke_time_advance.mlir:9-51`, `lib/Passes/HighLevelConvertion.cpp:77-120`): an operator definition
+    `@L` (class-S Laplacian, the reference's own body generalised to `rank` dimensions), a call
+    `apply_linear @L(%u)`, and an AXPY apply over (u, L(u)):
+
+        l  = dxinv2 * ((((n0 - k*u) + n1) + n2) + ...)        // @L
+        u' = u + dt * l                                        // apply(%u0, %l), both read at offset 0
+
+    Unfused this is two sweeps and a temporary; the `neptuneir-to-b200` pipeline folds it into one
+    (frontend/fusion.cpp)."""
+    rank = len(shape)
+    hdr, lb_, ub_ = _header(shape, ty)
+    ilb, iub = _interior(lb_, ub_)
+    offs = star_offsets(rank)
+    mr = _memref(rank, ty)
+    idx = ", ".join("%%i%d: index" % d for d in range(rank))
+    zero = _off([0] * rank)
+    L = ["  neptune_ir.linear_opdef @L : (!temp) -> !temp {",
+         "  ^bb0(%x: !temp):",
+         "    %%lap = neptune_ir.apply(%%x) attributes {bounds = %s} : (!temp) -> !temp {" % _bounds(ilb, iub),
+         "      ^bb0(%s, %%a0: !temp):" % idx,
+         "        %%c = neptune_ir.access %%a0%s : !temp -> %s" % (zero, ty)]
+    for j, o in enumerate(offs):
+        L.append("        %%n%d = neptune_ir.access %%a0%s : !temp -> %s" % (j, _off(o), ty))
+    L.append("        %%k = arith.constant %s : %s" % (_f(2.0 * rank, ty), ty))
+    L.append("        %%s = arith.constant %s : %s" % (_f(dxinv2, ty), ty))
+    L.append("        %%t0 = arith.mulf %%k, %%c : %s" % ty)
+    L.append("        %%t1 = arith.subf %%n0, %%t0 : %s" % ty)
+    for j in range(1, len(offs)):
+        L.append("        %%t%d = arith.addf %%t%d, %%n%d : %s" % (j + 1, j, j, ty))
+    L.append("        %%l = arith.mulf %%s, %%t%d : %s" % (len(offs), ty))
+    L.append("        neptune_ir.yield %%l : %s" % ty)
+    L.append("    }")
+    L.append("    neptune_ir.return %lap : !temp")
+    L.append("  }")
+    E = ["  func.func @entry(%%out: %s, %%in: %s) -> %s {" % (mr, mr, mr),
+         "    %%fout = neptune_ir.wrap %%out : %s -> !field" % mr,
+         "    %%fin  = neptune_ir.wrap %%in  : %s -> !field" % mr,
+         "    %u0   = neptune_ir.load %fin : !field -> !temp",
+         "    %lu   = neptune_ir.apply_linear @L(%u0) : (!temp) -> !temp",
+         "    %%r = neptune_ir.apply(%%u0, %%lu) attributes {bounds = %s} : (!temp, !temp) -> !temp {" % _bounds(ilb, iub),
+         "      ^bb0(%s, %%a0: !temp, %%a1: !temp):" % idx,
+         "        %%x0 = neptune_ir.access %%a0%s : !temp -> %s" % (zero, ty),
+         "        %%l0 = neptune_ir.access %%a1%s : !temp -> %s" % (zero, ty),
+         "        %%dt = arith.constant %s : %s" % (_f(dt, ty), ty),
+         "        %%t = arith.mulf %%dt, %%l0 : %s" % ty,
+         "        %%o = arith.addf %%x0, %%t : %s" % ty,
+         "        neptune_ir.yield %%o : %s" % ty,
+         "    }",
+         "    neptune_ir.store %r to %fout : !temp to !field",
+         "    %%res = neptune_ir.unwrap %%fout : !field -> %s" % mr,
+         "    func.return %%res : %s" % mr,
+         "  }"]
+    return hdr + "module {\n" + "\n".join(L) + "\n" + "\n".join(E) + "\n}\n"

@@ -162,3 +162,46 @@ def test_reduce_is_planned_and_other_kinds_rejected(nb):
     with pytest.raises(nb.NeptuneError) as e:
         nb.Module(H.mb.field_sum([8, 8], "f64").replace('"sum"', '"l2"'))
     assert "EUNSUPPORTED" in str(e.value) and "l2" in str(e.value)
+
+
+def test_operator_call_plus_axpy_is_fused_into_one_sweep(nb):
+    """`%l = apply_linear @L(%u); %r = apply(%u, %l){u + dt*l}` (the reference's explicit-step
+    composition, test/smoke_tests/smoke_time_advance.mlir:33-51) becomes ONE apply whose body is @L's op
+    list followed by the AXPY's; `fuse=false` keeps the two sweeps."""
+    for shape in ([16], [12, 16], [8, 8, 8]):
+        text = H.mb.euler_opdef(shape, 100.0, 1e-3)
+        m = nb.Module(text)
+        plan = m.plan("@entry")
+        assert "fused into one sweep" in plan and "call @L" not in plan
+        fused = [i for i in range(m.apply_count()) if m.apply_function(i) == "@entry"]
+        assert len(fused) == 1
+        d = m.apply_desc(fused[0])
+        assert d.n_inputs == 1 and nb.body_compiled(d.key())
+        src = m.cuda_source(fused[0])
+        assert src.count("A::mul(") == 3 and "tap<1," not in src     # k*c, s*(...), dt*l — and no second input
+        m.destroy()
+        m = nb.Module(text, "neptuneir-to-b200{fuse=false}")
+        plan = m.plan("@entry")
+        assert "call @L" in plan and "fused into one sweep" not in plan
+        m.destroy()
+    with pytest.raises(nb.NeptuneError):
+        nb.Module(H.mb.euler_opdef([8, 8], 1.0, 0.1), "neptuneir-to-b200{fuse=maybe}")
+
+
+def test_fusion_is_refused_when_it_would_change_the_result(nb):
+    """The temp must be read at offset 0 only, must not be input 0 (the copy-through source), and the
+    consumer's bounds must lie inside the producer's."""
+    text = H.mb.euler_opdef([12, 16], 100.0, 1e-3)
+    # consumer reads the operator's result at a neighbour offset
+    t1 = text.replace("%l0 = neptune_ir.access %a1[0, 0]", "%l0 = neptune_ir.access %a1[0, 1]")
+    # consumer bounds wider than the operator's: there %lu holds copy-through values
+    t2 = text.replace("neptune_ir.apply(%x) attributes {bounds = #neptune_ir.bounds<lb = [1, 1], ub = [11, 15]>}",
+                      "neptune_ir.apply(%x) attributes {bounds = #neptune_ir.bounds<lb = [2, 2], ub = [10, 14]>}")
+    assert t1 != text and t2 != text
+    for t in (t1, t2):
+        try:
+            m = nb.Module(t)
+        except nb.NeptuneError:
+            continue            # unfused AXPY-at-an-offset body is not in the catalogue: loud, not wrong
+        assert "fused into one sweep" not in m.plan("@entry")
+        m.destroy()

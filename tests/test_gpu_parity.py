@@ -583,3 +583,35 @@ def test_sweep_then_reduce_program_on_device(nb, ctx):
     assert H.bits_equal(out, want_out)
     inner = want_out[1:-1, 1:-1, 1:-1]
     assert abs(got[0] - want_s) <= inner.size * 2.2e-16 * float(np.sum(np.abs(inner)))
+
+
+@pytest.mark.parametrize("shape,ty,steps", [
+    ((64,), "f64", 5),
+    ((48, 512), "f64", 6),
+    ((24, 40, 136), "f64", 6),
+    ((20, 24, 64), "f32", 4),
+])
+def test_fused_operator_call_plus_axpy_bit_exact(nb, ctx, shape, ty, steps):
+    """N3: the explicit Euler step composed as `apply_linear @L` + AXPY apply runs as ONE fused sweep on
+    the device and equals the oracle, which executes the two applies one after the other (bit-exact: the
+    fused body is the same ops in the same order per point); so does the unfused device plan."""
+    if ty == "f32" and len(shape) != 3:
+        pytest.skip("catalogue ships the f32 fused body for rank 3 only")
+    text = H.mb.euler_opdef(list(shape), 100.0, 1e-3, ty)
+    u, _ = H.inputs(shape, 0, ty, seed=91)
+    want1 = H.oracle_entry(text, u, [])
+    want = H.oracle_steps(text, u, [], steps)
+    for pipeline, launches in (("neptuneir-to-b200", 1), ("neptuneir-to-b200{fuse=false}", 2)):
+        m = nb.Module(text, pipeline)
+        try:
+            out = np.full_like(u, np.nan)
+            n0 = ctx.launch_count()
+            m.run(ctx, "@entry", [out, u.copy()])
+            assert ctx.launch_count() - n0 == launches, pipeline
+            assert H.bits_equal(out, want1), pipeline
+            if launches == 1:
+                a, b = u.copy(), np.zeros_like(u)
+                res = m.run_steps(ctx, "@entry", [b, a], steps)
+                assert H.bits_equal([b, a][res], want), "time loop"
+        finally:
+            m.destroy()
