@@ -1,0 +1,24 @@
+#!/bin/bash
+# session K (1 GPU): full GPU suite, smoke, complete default bench line + reference arm, per-config lines, launch list
+mkdir -p gpurun_out
+timeout 1500 python -m pytest tests -m gpu -q -x > gpurun_out/pytest_gpu.log 2>&1; echo "pytest exit $?"; tail -6 gpurun_out/pytest_gpu.log
+timeout 600 python __graft_entry__.py --smoke > gpurun_out/smoke.log 2>&1; echo "smoke exit $?"; tail -2 gpurun_out/smoke.log
+timeout 900 python bench.py > gpurun_out/bench_default_full.json 2> gpurun_out/bench_default_full.err; echo "bench exit $?"; tail -3 gpurun_out/bench_default_full.err
+timeout 600 python bench.py --impl reference --steps 3 --warmup 1 > gpurun_out/bench_reference.json 2> gpurun_out/bench_reference.err; echo "ref exit $?"
+summ() { python - "$1" "$2" <<'PY'
+import json,sys
+try:
+    d=json.loads(open(sys.argv[2]).read().strip().splitlines()[-1]); r=d["roofline"]
+    print(sys.argv[1], d["config"]["kernel_variant"], "%.1f Gupd/s"%d["value"], "%.0f GB/s"%r["achieved"], "frac %.3f"%r["frac"], "ms %.4f"%d["ms_per_step"], "e2e", (d.get("e2e") or {}).get("value"), "cpu", (d.get("cpu_baseline") or {}).get("value"), "single", (r.get("single_step_kernel") or {}).get("value"))
+except Exception as e: print(sys.argv[1], "failed", e)
+PY
+}
+summ default gpurun_out/bench_default_full.json
+for w in c1 c2 c5 c5f32; do
+  f=gpurun_out/bench_${w}_full.json
+  timeout 600 python bench.py --workload $w --steps 40 --warmup 6 --e2e-steps 3 --cpu-seconds 8 > $f 2> gpurun_out/bench_${w}_full.err; summ "$w" $f; tail -2 gpurun_out/bench_${w}_full.err | cut -c1-200
+done
+f=gpurun_out/bench_c4_full.json
+timeout 900 python bench.py --workload c4 --steps 12 --warmup 3 --e2e-steps 0 --no-cpu > $f 2> gpurun_out/bench_c4_full.err; summ c4 $f
+CMD="python bench.py --steps 8 --warmup 3 --no-cpu --e2e-steps 1"
+timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/launches_default.csv $CMD > gpurun_out/ncu_list.log 2>&1; echo "ncu list exit $?"

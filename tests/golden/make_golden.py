@@ -23,6 +23,8 @@ CASES = [  # name, shape, dtype, steps, lb
     ("jacobi_star", (10, 12, 16), "f32", 12, None),    # C5 body f32
     ("heat_star", (40,), "f64", 20, (7,)),
     ("weighted_3d27", (8, 9, 10), "f64", 2, (3, -2, 5)),
+    ("euler_opdef", (10, 12, 16), "f64", 6, None),     # apply_linear @L + AXPY apply (N3)
+    ("euler_opdef", (24, 32), "f64", 6, None),
 ]
 
 

@@ -30,6 +30,9 @@ def program(name, shape, ty="f64", lb=None):
         return mb.heat_box_2d9(shape, 0.1, ty, lb), 0
     if name == "jacobi_star":
         return mb.jacobi_star(shape, 1.0 / (max(shape) ** 2), ty, lb), 1
+    if name == "euler_opdef":      # operator call + AXPY apply (two applies; fused on the device path)
+        assert lb is None
+        return mb.euler_opdef(shape, 100.0, 1e-3, ty), 0
     if name == "laplacian_s_1d":
         assert lb is None
         return mb.laplacian_s_1d(shape[0], 100.0, ty), 0
