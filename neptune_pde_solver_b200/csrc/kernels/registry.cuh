@@ -8,6 +8,7 @@
 #include "sweep_tma.cuh"
 #include "sweep_tb2.cuh"
 #include "sweep_tb2m.cuh"
+#include "sweep_tb2g.cuh"
 #include "sweep_rows.cuh"
 #include "sweep_rows2.cuh"
 
@@ -98,10 +99,16 @@ template <class F, class C, bool FMA> int launch_tma(const SweepArgs &a) {
   return (int)cudaGetLastError();
 }
 
-template <class F, class C, bool FMA, bool MARCH = false> int launch_tb2(const SweepArgs &a) {
-  typedef typename std::conditional<MARCH, Tb2mGeom<F, C>, Tb2Geom<F, C>>::type G;
+// MARCH: 0 = sweep_tb2 (both levels through shared memory), 1 = sweep_tb2m (z-marching), 2 = sweep_tb2g (z-marching, grouped)
+template <class F, class C, int MARCH> struct Tb2GeomOf { typedef Tb2Geom<F, C> type; };
+template <class F, class C> struct Tb2GeomOf<F, C, 1> { typedef Tb2mGeom<F, C> type; };
+template <class F, class C> struct Tb2GeomOf<F, C, 2> { typedef Tb2gGeom<F, C> type; };
+
+template <class F, class C, bool FMA, int MARCH = 0> int launch_tb2(const SweepArgs &a) {
+  typedef typename Tb2GeomOf<F, C, MARCH>::type G;
   auto kernel = [] {
-    if constexpr (MARCH) return sweep_tb2m<F, C, FMA>;
+    if constexpr (MARCH == 1) return sweep_tb2m<F, C, FMA>;
+    else if constexpr (MARCH == 2) return sweep_tb2g<F, C, FMA>;
     else return sweep_tb2<F, C, FMA>;
   }();
   static int occ_cached[16] = {0};
@@ -134,7 +141,7 @@ template <class F, class C, bool FMA, bool MARCH = false> int launch_tb2(const S
   if (items > 0x7fffffffLL) return (int)cudaErrorInvalidConfiguration;
   p.nitems = (int)items;
   const int grid = (int)std::min<long long>(items, slots);
-  if constexpr (MARCH) {
+  if constexpr (MARCH == 1) {
     if (F::NIN > 1 && !a.tmap_pw) return (int)cudaErrorInvalidValue;
     kernel<<<grid, G::THREADS, G::SMEM_BYTES, a.stream>>>(p, *a.tmap, a.tmap_pw ? *a.tmap_pw : *a.tmap);
   } else {
@@ -241,8 +248,8 @@ template <class F, class C, bool FMA> Variant rows2_variant(const char *name) {
   return v;
 }
 
-template <class F, class C, bool FMA, bool MARCH = false> Variant tb2_variant(const char *name) {
-  typedef typename std::conditional<MARCH, Tb2mGeom<F, C>, Tb2Geom<F, C>>::type G;
+template <class F, class C, bool FMA, int MARCH = 0> Variant tb2_variant(const char *name) {
+  typedef typename Tb2GeomOf<F, C, MARCH>::type G;
   Variant v;
   v.name = name;
   v.kind = VARIANT_TB2;
@@ -336,18 +343,20 @@ template <class F> struct BodyRegistrar {
           e.variants.push_back(tb2_variant<F, Tb2C, false>("tb2:128x16"));
           e.variants.push_back(tb2_variant<F, Tb2D, false>("tb2:64x32"));
           if constexpr (F::ZSTAR) {
-            e.variants.push_back(tb2_variant<F, Tb2mA, false, true>("tb2m:128x14"));
-            e.variants.push_back(tb2_variant<F, Tb2mA, true, true>("tb2m:128x14"));
-            e.variants.push_back(tb2_variant<F, Tb2mB, false, true>("tb2m:64x16"));
-            e.variants.push_back(tb2_variant<F, Tb2mC, false, true>("tb2m:128x14n8"));
-            e.variants.push_back(tb2_variant<F, Tb2mD, false, true>("tb2m:64x24"));
+            e.variants.push_back(tb2_variant<F, Tb2mA, false, 1>("tb2m:128x14"));
+            e.variants.push_back(tb2_variant<F, Tb2mA, true, 1>("tb2m:128x14"));
+            e.variants.push_back(tb2_variant<F, Tb2mB, false, 1>("tb2m:64x16"));
+            e.variants.push_back(tb2_variant<F, Tb2mC, false, 1>("tb2m:128x14n8"));
+            e.variants.push_back(tb2_variant<F, Tb2mD, false, 1>("tb2m:64x24"));
+            e.variants.push_back(tb2_variant<F, Tb2mA, false, 2>("tb2g:128x14"));
+            e.variants.push_back(tb2_variant<F, Tb2mD, false, 2>("tb2g:64x24"));
           }
         } else if constexpr (F::NIN == 2 && F::RZ == 1 && F::ZSTAR) {
           // input 0 plus pointwise inputs (Jacobi with a right-hand side): the z-marching form only
-          e.variants.push_back(tb2_variant<F, Tb2mG, false, true>("tb2m:64x24"));
-          e.variants.push_back(tb2_variant<F, Tb2mG, true, true>("tb2m:64x24"));
-          e.variants.push_back(tb2_variant<F, Tb2mE, false, true>("tb2m:128x10"));
-          e.variants.push_back(tb2_variant<F, Tb2mF, false, true>("tb2m:128x14"));
+          e.variants.push_back(tb2_variant<F, Tb2mG, false, 1>("tb2m:64x24"));
+          e.variants.push_back(tb2_variant<F, Tb2mG, true, 1>("tb2m:64x24"));
+          e.variants.push_back(tb2_variant<F, Tb2mE, false, 1>("tb2m:128x10"));
+          e.variants.push_back(tb2_variant<F, Tb2mF, false, 1>("tb2m:128x14"));
         }
       } else {
         if constexpr (F::RANK == 2 && F::RY == 1 && F::NIN <= 4) {
