@@ -115,6 +115,13 @@ int neptune_rt_timer_stop(neptune_rt_ctx *ctx, double *ms);
 int neptune_rt_field_alloc(neptune_rt_ctx *ctx, int dtype, int rank, const int64_t *lb,
                            const int64_t *ub, neptune_rt_field **field);
 int neptune_rt_field_free(neptune_rt_field *field);
+/* A field over device memory the CALLER owns (row-major box ub - lb, numel * sizeof(elem) bytes; 16-byte
+ * aligned rows let the staged kernels run, anything else takes the direct kernel). Not freed by
+ * neptune_rt_field_free. The matrix-free `y = A(x)` hook: the reference applies operators inside its Krylov
+ * solves through a MatShell callback on host vectors (NeptunePETScRuntime.cpp:182-230, MatMultThunk); a
+ * device-resident solver wraps its work vectors once and calls neptune_rt_apply. */
+int neptune_rt_field_wrap_device(neptune_rt_ctx *ctx, int dtype, int rank, const int64_t *lb,
+                                 const int64_t *ub, void *device_ptr, neptune_rt_field **field);
 /* Whole-box copies between a contiguous row-major host buffer and the field (async on the ctx
  * stream; host memory should be pinned for full PCIe speed).  */
 int neptune_rt_field_upload(neptune_rt_field *field, const void *host);

@@ -115,6 +115,7 @@ struct neptune_rt_field {
   int64_t ext[3] = {1, 1, 1};  // canonical (z, y, x)
   void *dptr = nullptr;
   size_t bytes = 0;
+  bool owned = true;   // false: caller's device memory (neptune_rt_field_wrap_device)
   size_t elsize() const { return dtype == NEPTUNE_RT_F64 ? 8 : 4; }
   int64_t numel() const { return ext[0] * ext[1] * ext[2]; }
 };
@@ -388,8 +389,38 @@ extern "C" int neptune_rt_field_free(neptune_rt_field *f) {
   if (!f) return NEPTUNE_RT_OK;
   cudaSetDevice(f->ctx->device);
   cudaStreamSynchronize(f->ctx->stream);
-  cudaFree(f->dptr);
+  if (f->owned) cudaFree(f->dptr);
   delete f;
+  return NEPTUNE_RT_OK;
+}
+
+// A field over device memory the caller owns (a solver's work vector, a torch tensor's data_ptr): the
+// matrix-free `y = A(x)` hook of SURVEY.md §8f N4 — the reference applies its operators through a MatShell
+// callback on host vectors (NeptunePETScRuntime.cpp:182-230); a device-resident Krylov loop calls
+// neptune_rt_apply on wrapped vectors instead, with no copy.
+extern "C" int neptune_rt_field_wrap_device(neptune_rt_ctx *c, int dtype, int rank, const int64_t *lb, const int64_t *ub,
+                                            void *device_ptr, neptune_rt_field **out) {
+  if (!c || !out || !lb || !ub || !device_ptr) return set_error(c, NEPTUNE_RT_EINVAL, "neptune_rt_field_wrap_device: NULL argument");
+  *out = nullptr;
+  if (rank < 1 || rank > NEPTUNE_RT_MAX_RANK) return set_error(c, NEPTUNE_RT_EINVAL, "field rank %d (1..3)", rank);
+  if (dtype != NEPTUNE_RT_F32 && dtype != NEPTUNE_RT_F64) return set_error(c, NEPTUNE_RT_EINVAL, "field dtype %d", dtype);
+  cudaPointerAttributes attr;
+  cudaSetDevice(c->device);
+  if (cudaPointerGetAttributes(&attr, device_ptr) != cudaSuccess || attr.type != cudaMemoryTypeDevice || attr.device != c->device) {
+    cudaGetLastError();
+    return set_error(c, NEPTUNE_RT_EINVAL, "neptune_rt_field_wrap_device: pointer is not device memory of GPU %d", c->device);
+  }
+  neptune_rt_field *f = new neptune_rt_field();
+  f->ctx = c; f->dtype = dtype; f->rank = rank; f->owned = false;
+  for (int d = 0; d < rank; ++d) {
+    if (ub[d] < lb[d] || ub[d] - lb[d] > 0x7fffffffLL) { delete f; return set_error(c, NEPTUNE_RT_EINVAL, "field bounds in dim %d", d); }
+    f->lb[d] = lb[d]; f->ub[d] = ub[d];
+  }
+  int64_t clb[3];
+  canon_box(rank, lb, ub, clb, f->ext);
+  f->bytes = (size_t)f->numel() * f->elsize();
+  f->dptr = device_ptr;
+  *out = f;
   return NEPTUNE_RT_OK;
 }
 

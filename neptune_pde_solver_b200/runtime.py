@@ -83,6 +83,7 @@ def lib() -> C.CDLL:
         "neptune_rt_field_upload_planes": (i32, [vp, vp, i64, i64]),
         "neptune_rt_field_download_planes": (i32, [vp, vp, i64, i64]),
         "neptune_rt_field_fill": (i32, [vp, C.c_double]),
+        "neptune_rt_field_wrap_device": (i32, [vp, i32, i32, i64p, i64p, vp, C.POINTER(vp)]),
         "neptune_rt_field_device_ptr": (vp, [vp]),
         "neptune_rt_field_bytes": (i64, [vp]),
         "neptune_rt_field_store": (i32, [vp, vp, i64p, i64p]),
@@ -282,6 +283,20 @@ class Field:
         lb = [0] * a.ndim if lb is None else list(lb)
         f = cls(ctx, a.dtype, lb, [l + n for l, n in zip(lb, a.shape)])
         f.upload(a)
+        return f
+
+    @classmethod
+    def wrap_device(cls, ctx: Context, device_ptr: int, dtype, shape: Sequence[int], lb: Optional[Sequence[int]] = None) -> "Field":
+        """A field over device memory the caller owns (e.g. `tensor.data_ptr()` of a contiguous CUDA tensor)."""
+        lb = [0] * len(shape) if lb is None else list(lb)
+        ub = [l + int(n) for l, n in zip(lb, shape)]
+        f = cls.__new__(cls)
+        f.ctx = ctx
+        f.dtype = dtype if isinstance(dtype, int) else _DT[np.dtype(dtype)]
+        f.lb, f.ub = [int(x) for x in lb], [int(x) for x in ub]
+        f.shape = tuple(int(n) for n in shape)
+        f.h = C.c_void_p()
+        ctx._check(ctx._L.neptune_rt_field_wrap_device(ctx.h, f.dtype, len(shape), _i64(f.lb), _i64(f.ub), C.c_void_p(device_ptr), C.byref(f.h)))
         return f
 
     def _host(self, a: np.ndarray) -> np.ndarray:

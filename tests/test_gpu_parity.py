@@ -707,3 +707,44 @@ def test_full_size_properties(nb, ctx, name, shape):
     else:
         got = fused[mid - 8:mid + 8, :4096]
         assert H.bits_equal(got[4:12, :4092], want[4:12, :4092])
+
+
+def test_matrix_free_operator_on_caller_owned_device_vectors(nb, ctx):
+    """`y = A(x)` on device memory the caller owns (torch CUDA tensors here), the hook a
+    device-resident Krylov loop needs — no copies, same kernels, same bits as the oracle.  A few steps of a
+    matrix-free Richardson iteration x <- x + w (b - A x) run entirely on the device with torch doing the
+    vector algebra; every A(x) is checked against the oracle."""
+    import torch
+    shape = (24, 40, 136)
+    lap = H.mb.weighted_const(list(shape), H.STAR7, [6.0, -1.0, -1.0, -1.0, -1.0, -1.0, -1.0])   # A = -Laplacian (class L body)
+    m = nb.Module(lap)
+    try:
+        st = m.stencil(ctx, 0)
+        dev = torch.device("cuda", 0)
+        rng = np.random.default_rng(61)
+        x_h = rng.uniform(-1, 1, size=shape)
+        b_h = rng.uniform(-1, 1, size=shape)
+        x = torch.from_numpy(x_h).to(dev)
+        b = torch.from_numpy(b_h).to(dev)
+        y = torch.empty_like(x)
+        fx = nb.Field.wrap_device(ctx, x.data_ptr(), np.float64, shape)
+        fy = nb.Field.wrap_device(ctx, y.data_ptr(), np.float64, shape)
+        torch.cuda.synchronize()
+        for it in range(3):
+            st.apply([fx], fy)                    # y = A(x): interior = -Lap(x), shell = x (copy-through)
+            ctx.sync()
+            want = H.oracle_entry(lap, x.cpu().numpy(), [])
+            assert H.bits_equal(y.cpu().numpy(), want), "A(x) differs at iteration %d" % it
+            assert st.variant().startswith("tma")
+            r = b - y
+            r[0], r[-1] = 0, 0; r[:, 0], r[:, -1] = 0, 0; r[:, :, 0], r[:, :, -1] = 0, 0   # Dirichlet shell
+            x += 0.08 * r                         # in place: fx still wraps x's memory
+            torch.cuda.synchronize()
+        fx.free(); fy.free()
+        # the wrapped tensors are still alive and untouched by free()
+        assert torch.isfinite(x).all() and torch.isfinite(y).all()
+        # host memory is refused loudly
+        with pytest.raises(nb.NeptuneError):
+            nb.Field.wrap_device(ctx, x_h.ctypes.data, np.float64, shape)
+    finally:
+        m.destroy()
