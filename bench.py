@@ -449,7 +449,8 @@ def run_b200(args):
             "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": ty, "data": "synthetic",
             "config": {"workload": descr, "grid_per_gpu": list(shape1), "global_grid": gshape,
-                       "decomposition": "dim-0 slabs, 1 ghost plane, NCCL send/recv overlapped with interior" if world > 1 else "single domain",
+                       "decomposition": ("dim-0 slabs, %d ghost plane(s) per neighbour side, one NCCL send/recv exchange per %s overlapped with the interior sweep"
+                                         % (slab.halo, "fused pair of steps" if variant.startswith("tb2") else "step")) if world > 1 else "single domain",
                        "points_per_step": int(total_points), "kernel_variant": variant,
                        "l2": "inputs larger than L2 (%.2f GB per field vs 126 MB L2); no flush needed" % (field_bytes / 1e9),
                        "fma": False, "parity": "bit-exact vs oracle (tests/test_gpu_parity.py)"},
