@@ -885,9 +885,15 @@ extern "C" int neptune_rt_apply_host(neptune_rt_stencil *s, int n_in, neptune_rt
   for (int k = 0; k < n_in; ++k)
     same_rows &= in[k] && in[k]->rank == out->rank && in[k]->lb[0] == out->lb[0] && in[k]->ub[0] == out->ub[0];
   if (chunk_planes <= 0) {
-    // about 16 chunks, at least 8 MiB each so that a copy runs at full PCIe rate
+    // about `target` chunks (pipeline fill and drain cost about 3 / target of the transfer time), at least
+    // 8 MiB each so that a copy runs at full PCIe rate; NEPTUNE_RT_HOST_CHUNKS overrides the target
+    static const int64_t target = [] {
+      const char *e = std::getenv("NEPTUNE_RT_HOST_CHUNKS");
+      const long v = e ? std::atol(e) : 0;
+      return (int64_t)(v >= 3 && v <= 4096 ? v : 32);   // r01, C3: 16 -> 24.7 ms, 32 -> 23.5, 64 -> 23.6, 128 -> 25.0 (PCIe: 46 GB/s each way)
+    }();
     const size_t plane = n0 ? out->bytes / (size_t)n0 : 1;
-    chunk_planes = std::max<int64_t>((n0 + 15) / 16, (int64_t)(((size_t)8 << 20) + plane - 1) / (int64_t)std::max<size_t>(plane, 1));
+    chunk_planes = std::max<int64_t>((n0 + target - 1) / target, (int64_t)(((size_t)8 << 20) + plane - 1) / (int64_t)std::max<size_t>(plane, 1));
   }
   chunk_planes = std::max<int64_t>(chunk_planes, std::max<int64_t>(radius, 1));
   const int64_t nchunks = n0 > 0 ? (n0 + chunk_planes - 1) / chunk_planes : 0;
