@@ -480,7 +480,9 @@ def main():
     ap.add_argument("--e2e-steps", type=int, default=10)
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
     ap.add_argument("--no-cpu", action="store_true")
-    ap.add_argument("--omp-context", action="store_true")
+    ap.add_argument("--omp-context", dest="omp_context", action="store_true", default=True,
+                    help="also report a best-effort all-core OpenMP CPU number beside the faithful 1-thread reference lowering (context, not the reference)")
+    ap.add_argument("--no-omp-context", dest="omp_context", action="store_false")
     ap.add_argument("--traffic", type=float, default=None,
                     help="dram bytes per launch from the committed ncu --set full capture (profiles/)")
     args = ap.parse_args()
