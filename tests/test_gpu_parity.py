@@ -748,3 +748,37 @@ def test_matrix_free_operator_on_caller_owned_device_vectors(nb, ctx):
             nb.Field.wrap_device(ctx, x_h.ctypes.data, np.float64, shape)
     finally:
         m.destroy()
+
+
+@pytest.mark.parametrize("name,shape,variants", [
+    ("heat_star", (96, 112, 256), ["tb2:128x16", "tb2m:128x14", "tb2g:128x14", "tb2m:64x24"]),
+    ("heat_box_2d9", (1536, 2032), ["tb2r:256x3", "tb2r:512x3"]),
+    ("jacobi_star", (96, 96, 192), ["tb2m:64x24", "tb2m:128x14"]),
+])
+def test_temporally_blocked_kernels_repeat_bitwise(nb, ctx, name, shape, variants):
+    """compute-sanitizer's racecheck is not available on the pool, so shared-memory hazards of the kernels that
+    exchange level-1 values between threads are hunted the blunt way: sizes with many CTAs per SM slot and
+    several items per CTA, 12 repetitions per kernel, every result compared bitwise with the single-step
+    kernel's (which has no inter-thread exchange).  A missing barrier shows up as a flaky mismatch."""
+    text, n_extra = H.program(name, list(shape))
+    u, extra = H.inputs(shape, n_extra, "f64", seed=73)
+    m = nb.Module(text)
+    try:
+        st = m.stencil(ctx, 0)
+        fx = [nb.Field.from_numpy(ctx, e) for e in extra]
+        st.set("tblock", 1)
+        fa, fb = nb.Field.from_numpy(ctx, u), nb.Field.from_numpy(ctx, u)
+        want = st.run_steps(fa, fb, fx, 6).download()
+        st.set("tblock", 0)
+        for v in variants:
+            st.set("variant", v)
+            for rep in range(12):
+                st.set("zchunk", str([0, 16, 24, 33][rep % 4]))
+                fa.upload(u); fb.upload(u)
+                got = st.run_steps(fa, fb, fx, 6).download()
+                assert st.variant() == v
+                assert H.bits_equal(got, want), "%s repetition %d differs" % (v, rep)
+        for f in [fa, fb] + fx:
+            f.free()
+    finally:
+        m.destroy()
