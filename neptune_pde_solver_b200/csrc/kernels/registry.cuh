@@ -9,6 +9,7 @@
 #include "sweep_tb2.cuh"
 #include "sweep_tb2m.cuh"
 #include "sweep_tb2g.cuh"
+#include "sweep_tb2p.cuh"
 #include "sweep_rows.cuh"
 #include "sweep_rows2.cuh"
 
@@ -99,16 +100,19 @@ template <class F, class C, bool FMA> int launch_tma(const SweepArgs &a) {
   return (int)cudaGetLastError();
 }
 
-// MARCH: 0 = sweep_tb2 (both levels through shared memory), 1 = sweep_tb2m (z-marching), 2 = sweep_tb2g (z-marching, grouped)
+// MARCH: 0 = sweep_tb2 (both levels through shared memory), 1 = sweep_tb2m (z-marching), 2 = sweep_tb2g (z-marching,
+// grouped), 3 = sweep_tb2p (grouped, phase B software-pipelined into phase A)
 template <class F, class C, int MARCH> struct Tb2GeomOf { typedef Tb2Geom<F, C> type; };
 template <class F, class C> struct Tb2GeomOf<F, C, 1> { typedef Tb2mGeom<F, C> type; };
 template <class F, class C> struct Tb2GeomOf<F, C, 2> { typedef Tb2gGeom<F, C> type; };
+template <class F, class C> struct Tb2GeomOf<F, C, 3> { typedef Tb2pGeom<F, C> type; };
 
 template <class F, class C, bool FMA, int MARCH = 0> int launch_tb2(const SweepArgs &a) {
   typedef typename Tb2GeomOf<F, C, MARCH>::type G;
   auto kernel = [] {
     if constexpr (MARCH == 1) return sweep_tb2m<F, C, FMA>;
     else if constexpr (MARCH == 2) return sweep_tb2g<F, C, FMA>;
+    else if constexpr (MARCH == 3) return sweep_tb2p<F, C, FMA>;
     else return sweep_tb2<F, C, FMA>;
   }();
   static int occ_cached[16] = {0};
@@ -294,6 +298,9 @@ typedef Tb2Cfg<128, 14, 2, 8, 1> Tb2mC;
 typedef Tb2Cfg<64, 24, 2, 8, 1> Tb2mD;
 typedef Tb2Cfg<128, 10, 2, 6, 1> Tb2mE;
 typedef Tb2Cfg<64, 24, 2, 5, 1> Tb2mG;
+typedef Tb2Cfg<128, 14, 2, 4, 1> Tb2pA;   // seven level-1 planes leave room for four level-0 slots
+typedef Tb2Cfg<64, 24, 2, 6, 1> Tb2pB;
+
 typedef Tb2Cfg<128, 14, 2, 4, 1> Tb2mF;   // two staged tiles per slot: four slots fit beside the level-1 planes
 typedef TileCfg<64, 8, 1, 6, 1> Tile3W;   // many-input bodies (one coefficient field per tap)
 typedef TileCfg<64, 7, 1, 6, 2> Tile3W2;  // 256 threads, two CTAs per SM at 128 registers
@@ -350,6 +357,9 @@ template <class F> struct BodyRegistrar {
             e.variants.push_back(tb2_variant<F, Tb2mD, false, 1>("tb2m:64x24"));
             e.variants.push_back(tb2_variant<F, Tb2mA, false, 2>("tb2g:128x14"));
             e.variants.push_back(tb2_variant<F, Tb2mD, false, 2>("tb2g:64x24"));
+            e.variants.push_back(tb2_variant<F, Tb2pA, false, 3>("tb2p:128x14"));
+            e.variants.push_back(tb2_variant<F, Tb2pB, false, 3>("tb2p:64x24"));
+            e.variants.push_back(tb2_variant<F, Tb2pA, true, 3>("tb2p:128x14"));
           }
         } else if constexpr (F::NIN == 2 && F::RZ == 1 && F::ZSTAR) {
           // input 0 plus pointwise inputs (Jacobi with a right-hand side): the z-marching form only

@@ -791,7 +791,12 @@ int do_apply(neptune_rt_stencil *s, int n_in, neptune_rt_field *const *in, neptu
       const bool wide = out->ext[2] >= 256;
       // two inputs (Jacobi + rhs, r01 768^3): f64 tb2m:64x24 383 / 128x10 340 / 128x14 323 Gupd/s; f32 128x14 536 / 64x24 464
       const char *two_in = d.dtype == NEPTUNE_RT_F64 ? "tb2m:64x24" : "tb2m:128x14";
-      const char *prefer[] = {n_in > 1 ? two_in : wide ? "tb2m:128x14" : "tb2:64x16", wide ? "tb2:128x16" : "tb2:64x16"};
+      // one input, wide box (r01, 512^3 f64): tb2p:128x14 466, tb2m:128x14 427, tb2g:128x14 415, tb2:128x16 409 Gupd/s.
+      // The pipelined form pays seven planes of fill and drain per item instead of four: thin launches (the
+      // boundary planes of a slab) keep tb2m.
+      const bool deep = p1 - p0 >= 24;
+      const char *prefer[] = {n_in > 1 ? two_in : wide ? (deep ? "tb2p:128x14" : "tb2m:128x14") : "tb2:64x16",
+                              wide ? "tb2m:128x14" : "tb2:64x16"};
       for (const char *name : prefer) {
         for (auto &v : s->body->variants)
           if (v.kind == neptune::VARIANT_TB2 && v.fma == s->fma && v.name == name) { pick = &v; break; }
