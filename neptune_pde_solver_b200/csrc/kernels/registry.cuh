@@ -298,8 +298,8 @@ typedef Tb2Cfg<128, 14, 2, 8, 1> Tb2mC;
 typedef Tb2Cfg<64, 24, 2, 8, 1> Tb2mD;
 typedef Tb2Cfg<128, 10, 2, 6, 1> Tb2mE;
 typedef Tb2Cfg<64, 24, 2, 5, 1> Tb2mG;
-typedef Tb2Cfg<128, 14, 2, 4, 1> Tb2pA;   // seven level-1 planes leave room for four level-0 slots
-typedef Tb2Cfg<64, 24, 2, 6, 1> Tb2pB;
+typedef Tb2pCfg<128, 14, 2, 4, 1, 3> Tb2pA;   // seven level-1 planes leave room for four level-0 slots
+typedef Tb2pCfg<64, 24, 2, 6, 1, 3> Tb2pB;
 
 typedef Tb2Cfg<128, 14, 2, 4, 1> Tb2mF;   // two staged tiles per slot: four slots fit beside the level-1 planes
 typedef TileCfg<64, 8, 1, 6, 1> Tile3W;   // many-input bodies (one coefficient field per tap)

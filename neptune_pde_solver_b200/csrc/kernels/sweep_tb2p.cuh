@@ -5,7 +5,7 @@
 // (profiles/r01_c3_tb2m_stall_breakdown.md).  Here phase B of the PREVIOUS group rides in the same steps as
 // phase A of the current one: step R of a group
 //     A : level-0 plane k arrives  -> level-1 plane k-1 (stored to the level-1 ring)
-//     B': level-2 plane k-5        <- level-1 planes k-6, k-5, k-4 (all produced before the last barrier)
+//     B': level-2 plane k-LAG        <- level-1 planes k-6, k-5, k-4 (all produced before the last barrier)
 // so both levels' chains interleave in one stream as in tb2m, with ONE consumer barrier per three planes and
 // no per-plane register moves.  The level-1 ring holds seven planes (the three being written, the four
 // being read); an item runs three extra steps (B' only) to drain.  Geometry, TMA producer, masks and
@@ -15,9 +15,19 @@
 
 namespace neptune {
 
+// GS = planes per barrier group (2 or 3).  Level-1 ring = 2*GS + 1 planes (GS being written, GS + 1 being read);
+// phase B' lags phase A by GS + 1 planes.  GS = 3 needs no register rotation with a 3-step loop body; GS = 2
+// unrolls six steps (three groups) for the same effect and leaves shared memory for two more level-0 TMA slots
+// — but ptxas spills 2.4 KB on the six-step body at 96 registers (r01), so only GS = 3 is registered.
+template <int TX_, int TY_, int VY_, int NS_, int MINB_, int GS_ = 3> struct Tb2pCfg : Tb2Cfg<TX_, TY_, VY_, NS_, MINB_> {
+  static constexpr int GS = GS_;
+};
+
 template <class F, class C> struct Tb2pGeom : Tb2mGeom<F, C> {
   typedef Tb2mGeom<F, C> B;
-  static constexpr int NL1 = 7;
+  static constexpr int GS = C::GS;
+  static constexpr int NL1 = 2 * GS + 1;
+  static_assert(GS == 2 || GS == 3, "two or three planes per barrier group");
   static constexpr int SMEM_BYTES = B::GUARD_BYTES + B::NS * B::SLOT_BYTES + B::GUARD_BYTES + B::L1_GUARD + NL1 * B::L1_BYTES +
                                     B::L1_GUARD + 2 * B::NS * 8 + 128;
   static_assert(F::NIN == 1, "pipelined grouped form: single-input bodies");
@@ -32,11 +42,14 @@ sweep_tb2p(const __grid_constant__ KParams<F> p, const __grid_constant__ CUtenso
   typedef typename F::T T;
   constexpr int VX = G::VX, VY = G::VY, NS = G::NS;
   constexpr int NCW = G::CONSUMERS / 32;
+  constexpr int GS = G::GS, NL1 = G::NL1;
+  constexpr int U = GS == 3 ? 3 : 6;     // steps per loop iteration: a multiple of GS and of the 3-deep z windows
+  constexpr int LAG = GS + 2;            // phase B' of a step computes level-2 plane k - LAG
 
   extern __shared__ __align__(128) unsigned char smem_raw[];
   unsigned char *smem = smem_raw + ((128u - (smem_u32(smem_raw) & 127u)) & 127u);
   unsigned char *l0 = smem + G::GUARD_BYTES;                                          // NS level-0 stages
-  unsigned char *l1 = l0 + NS * G::SLOT_BYTES + G::GUARD_BYTES + G::L1_GUARD;          // 7 level-1 planes
+  unsigned char *l1 = l0 + NS * G::SLOT_BYTES + G::GUARD_BYTES + G::L1_GUARD;          // 2*GS + 1 level-1 planes
   const uint32_t full0 = smem_u32(l1 + G::NL1 * G::L1_BYTES + G::L1_GUARD);
   const uint32_t empty0 = full0 + 8 * NS;
   const uint32_t stage0 = smem_u32(l0);
@@ -95,10 +108,10 @@ sweep_tb2p(const __grid_constant__ KParams<F> p, const __grid_constant__ CUtenso
   unsigned s = 0, ph = 0;   // level-0 ring slot / phase of the next plane to arrive
   unsigned c1 = 0;          // level-1 ring slot (0..6) phase A writes at the current step (advances every step with j >= 2)
   // z windows: a[R], a[R+1], a[R+2] = level-0 centre blocks of planes k-2, k-1, k at step R of a group;
-  // b[R], b[R+1], b[R+2] = level-1 centre blocks of planes k-6, k-5, k-4
-  T a[5][VY][VX], b[5][VY][VX];
+  // b[R], b[R+1], b[R+2] = level-1 centre blocks of planes k-LAG-1, k-LAG, k-LAG+1
+  T a[U + 2][VY][VX], b[U + 2][VY][VX];
 #pragma unroll
-  for (int q = 0; q < 5; ++q)
+  for (int q = 0; q < U + 2; ++q)
 #pragma unroll
     for (int iy = 0; iy < VY; ++iy)
 #pragma unroll
@@ -129,20 +142,20 @@ sweep_tb2p(const __grid_constant__ KParams<F> p, const __grid_constant__ CUtenso
 
     // one group of three steps j0, j0+1, j0+2; an item has nslots arrivals and three drain steps.
     // STEADY: every step has an arrival and j0 >= 7 (both phases live, no tests on j)
-    for (int j0 = 0; j0 < nslots + 3; j0 += 3) {
-      const bool steady = j0 >= 7 && j0 + 3 <= nslots;
+    for (int j0 = 0; j0 < nslots + GS; j0 += U) {
+      const bool steady = j0 >= LAG + 2 && j0 + U <= nslots;
       static_for<2>([&](auto steadyc) {
       constexpr bool STEADY = decltype(steadyc)::value == 1;
       if (steady != STEADY) return;
-      auto slot = [](unsigned base, unsigned d) { const unsigned v = base + d; return v >= 7u ? v - 7u : v; };
-      static_for<3>([&](auto rc) {
+      auto slot = [](unsigned base, unsigned d) { const unsigned v = base + d; return v >= (unsigned)NL1 ? v - (unsigned)NL1 : v; };
+      static_for<U>([&](auto rc) {
         constexpr int R = decltype(rc)::value;
         const int j = j0 + R;
         const int k = zb - 2 + j;
         const bool arrive = STEADY || j < nslots;        // a level-0 plane arrives at this step
         const bool do_a = STEADY || (arrive && j >= 2);  // ... and completes level-1 plane k-1
-        const bool push_b = STEADY || (j >= 5 && j < nslots + 3);   // level-1 plane k-4 exists
-        const bool do_b = STEADY || (j >= 7 && j < nslots + 3);     // level-2 plane k-5 is wanted
+        const bool push_b = STEADY || (j >= LAG && j < nslots + GS);       // level-1 plane k-LAG+1 exists
+        const bool do_b = STEADY || (j >= LAG + 2 && j < nslots + GS);     // level-2 plane k-LAG is wanted
         T wa[VY + 2][VX + 2], wb[VY + 2][VX + 2];
         // ---- level-0 reads ----------------------------------------------------------------------------
         if (arrive) {
@@ -180,14 +193,14 @@ sweep_tb2p(const __grid_constant__ KParams<F> p, const __grid_constant__ CUtenso
             stg_vec<T, VX, false>(l1p + IY * G::P1, ra);
           });
         }
-        // ---- phase B': level-2 plane k-5 -------------------------------------------------------------
+        // ---- phase B': level-2 plane k-LAG -------------------------------------------------------------
         // (its shared-memory reads come after phase A's arithmetic in program order, as in sweep_tb2m: reading
         // both windows up front keeps 12 more fp64 values live through phase A and spills at 96 registers)
         if (push_b && wmask != 0) {
-          const T *pnew = ring1 + slot(c1, 4u) * L1_ELEMS + soff1;   // level-1 plane k-4 (this thread's block): slot c1 - 3
+          const T *pnew = ring1 + slot(c1, GS + 1) * L1_ELEMS + soff1;   // level-1 plane k-LAG+1 (this thread's block): slot c1 - GS
 #pragma unroll
           for (int r = 0; r < VY; ++r) lds_vec<T, VX>(b[R + 2][r], pnew + r * G::P1);
-          if (do_b) load_halo<T, VX, VY, G::P1>(wb, ring1 + slot(c1, 3u) * L1_ELEMS + soff1, swap);   // plane k-5: slot c1 - 4
+          if (do_b) load_halo<T, VX, VY, G::P1>(wb, ring1 + slot(c1, GS) * L1_ELEMS + soff1, swap);   // plane k-LAG: slot c1 - GS - 1
         }
         if (do_b) {
           if (wmask != 0) {
@@ -195,7 +208,7 @@ sweep_tb2p(const __grid_constant__ KParams<F> p, const __grid_constant__ CUtenso
             for (int iy = 0; iy < VY; ++iy)
 #pragma unroll
               for (int ix = 0; ix < VX; ++ix) wb[1 + iy][1 + ix] = b[R + 1][iy][ix];
-            const unsigned m = (k - 5 >= p.blo[0] && k - 5 < p.bhi[0]) ? bmask : 0u;
+            const unsigned m = (k - LAG >= p.blo[0] && k - LAG < p.bhi[0]) ? bmask : 0u;
             static_for<VY>([&](auto iyc) {
               constexpr int IY = decltype(iyc)::value;
               T res[VX];
@@ -218,18 +231,18 @@ sweep_tb2p(const __grid_constant__ KParams<F> p, const __grid_constant__ CUtenso
           }
           dst += p.out_sz;
         }
-        if (STEADY || (j >= 2 && j < nslots + 3)) c1 = slot(c1, 1u);
+        if (STEADY || (j >= 2 && j < nslots + GS)) c1 = slot(c1, 1u);
+        // one barrier per group of GS steps: the group's level-1 planes become visible, and the planes phase B'
+        // read (the next group's writes, a full ring on) are free
+        if constexpr ((R + 1) % GS == 0) asm volatile("bar.sync 1, %0;" ::"n"(G::CONSUMERS) : "memory");
       });
-      // one barrier per group: this group's level-1 planes become visible, and the planes phase B' read
-      // (the next group's writes, seven slots on) are free
-      asm volatile("bar.sync 1, %0;" ::"n"(G::CONSUMERS) : "memory");
-      // rotate the windows by three planes (the only register moves of the group)
+      // rotate the windows by U planes (the only register moves of an iteration)
 #pragma unroll
       for (int q = 0; q < 2; ++q)
 #pragma unroll
         for (int iy = 0; iy < VY; ++iy)
 #pragma unroll
-          for (int ix = 0; ix < VX; ++ix) { a[q][iy][ix] = a[q + 3][iy][ix]; b[q][iy][ix] = b[q + 3][iy][ix]; }
+          for (int ix = 0; ix < VX; ++ix) { a[q][iy][ix] = a[q + U][iy][ix]; b[q][iy][ix] = b[q + U][iy][ix]; }
       });
     }
   }
