@@ -172,6 +172,11 @@ int neptune_rt_apply(neptune_rt_stencil *stencil, int n_in, neptune_rt_field *co
 /* Sweep only planes [p0, p1) of dim 0 of the result box (slab boundary / interior split). */
 int neptune_rt_apply_planes(neptune_rt_stencil *stencil, int n_in, neptune_rt_field *const *in,
                             neptune_rt_field *out, int64_t p0, int64_t p1, void *stream);
+/* Sweep planes [p0, g0) and [g1, p1) of dim 0 (equally wide, g0 < g1) and leave [g0, g1) alone: the two
+ * boundary ranges of a slab that has a neighbour on both sides, as ONE launch where the kernel variant
+ * takes two plane ranges (else as two). The slab time loop uses it before each halo exchange. */
+int neptune_rt_apply_planes2(neptune_rt_stencil *stencil, int n_in, neptune_rt_field *const *in,
+                             neptune_rt_field *out, int64_t p0, int64_t g0, int64_t g1, int64_t p1, void *stream);
 /* One sweep on HOST buffers, pipelined over dim-0 plane chunks: upload of chunk i+1, sweep of chunk
  * i and download of chunk i-1 run concurrently (two copy engines + SMs), so the call costs about
  * max(upload, download) instead of their sum. in_host[k] == NULL means input k is already resident

@@ -65,6 +65,7 @@ template <class F> struct KParams {
   int wlo[3], whi[3];    // box this launch writes (whole result box, or a slab of planes)
   // persistent-tile kernels only
   int zchunk, nchunks, ncx, ncy, cxo, cyo, nitems;
+  int zgap;              // planes skipped between chunk 0 and chunk 1 (two boundary ranges in one launch), else 0
   T c[F::NCONST > 0 ? F::NCONST : 1];
 };
 

@@ -27,7 +27,7 @@ template <class F> void fill_params(KParams<F> &p, const SweepArgs &a) {
   p.out_sz = a.out_sz; p.out_sy = a.out_sy;
   p.nz = a.nz; p.ny = a.ny; p.nx = a.nx;
   for (int d = 0; d < 3; ++d) { p.blo[d] = a.blo[d]; p.bhi[d] = a.bhi[d]; p.wlo[d] = a.wlo[d]; p.whi[d] = a.whi[d]; }
-  p.zchunk = p.nchunks = p.ncx = p.ncy = p.cxo = p.cyo = p.nitems = 0;
+  p.zchunk = p.nchunks = p.ncx = p.ncy = p.cxo = p.cyo = p.nitems = p.zgap = 0;
   for (int i = 0; i < F::NCONST; ++i) p.c[i] = (T)a.consts[i];
   if (F::NCONST == 0) p.c[0] = T(0);
 }
@@ -63,6 +63,17 @@ inline int choose_zchunk(int planes, int ncols, int grid_slots, int rz) {
   return best_zc;
 }
 
+// two boundary ranges [wlo, gap_lo) and [gap_hi, whi) of the marching dimension `dim` as chunks 0 and 1 of one launch
+template <class KP> inline bool set_gap(KP &p, const SweepArgs &a, int dim) {
+  if (a.gap_hi <= a.gap_lo) return true;
+  const int w = a.gap_lo - a.wlo[dim];
+  if (w <= 0 || a.whi[dim] - a.gap_hi != w) return false;
+  p.zchunk = w;
+  p.nchunks = 2;
+  p.zgap = a.gap_hi - a.gap_lo;
+  return true;
+}
+
 template <class F, class C, bool FMA> int launch_tma(const SweepArgs &a) {
   typedef TmaGeom<F, C> G;
   auto kernel = sweep_tma<F, C, FMA>;
@@ -92,6 +103,7 @@ template <class F, class C, bool FMA> int launch_tma(const SweepArgs &a) {
   const int slots = a.sm_count * occ_cached[dev];
   p.zchunk = a.zchunk > 0 ? std::min(a.zchunk, wz) : choose_zchunk(wz, ncols, slots, F::RZ);
   p.nchunks = (wz + p.zchunk - 1) / p.zchunk;
+  if (!set_gap(p, a, 0)) return (int)cudaErrorInvalidValue;
   const long long items = (long long)p.nchunks * ncols;
   if (items > 0x7fffffffLL) return (int)cudaErrorInvalidConfiguration;
   p.nitems = (int)items;
@@ -141,6 +153,7 @@ template <class F, class C, bool FMA, int MARCH = 0> int launch_tb2(const SweepA
   const int slots = a.sm_count * occ_cached[dev];
   p.zchunk = a.zchunk > 0 ? std::min(a.zchunk, wz) : choose_zchunk(wz, ncols, slots, 2);
   p.nchunks = (wz + p.zchunk - 1) / p.zchunk;
+  if (!set_gap(p, a, 0)) return (int)cudaErrorInvalidValue;
   const long long items = (long long)p.nchunks * ncols;
   if (items > 0x7fffffffLL) return (int)cudaErrorInvalidConfiguration;
   p.nitems = (int)items;
@@ -181,6 +194,7 @@ template <class F, class C, bool FMA> int launch_rows(const SweepArgs &a) {
   const int slots = a.sm_count * occ_cached[dev];
   p.zchunk = a.zchunk > 0 ? std::min(a.zchunk, wy) : choose_zchunk(wy, p.ncx, slots, 1);
   p.nchunks = (wy + p.zchunk - 1) / p.zchunk;
+  if (!set_gap(p, a, 1)) return (int)cudaErrorInvalidValue;
   const long long items = (long long)p.nchunks * p.ncx;
   if (items > 0x7fffffffLL) return (int)cudaErrorInvalidConfiguration;
   p.nitems = (int)items;
@@ -198,6 +212,7 @@ template <class F, class C, bool FMA> Variant rows_variant(const char *name) {
   v.tx = C::TX; v.ty = C::RB;
   v.halo_x = G::HX; v.halo_y = 1;
   v.threads = G::THREADS; v.smem = G::SMEM_BYTES;
+  v.gap_dim = 1;
   v.launch = &launch_rows<F, C, FMA>;
   return v;
 }
@@ -229,6 +244,7 @@ template <class F, class C, bool FMA> int launch_rows2(const SweepArgs &a) {
   const int slots = a.sm_count * occ_cached[dev];
   p.zchunk = a.zchunk > 0 ? std::min(a.zchunk, wy) : choose_zchunk(wy, p.ncx, slots, 2);
   p.nchunks = (wy + p.zchunk - 1) / p.zchunk;
+  if (!set_gap(p, a, 1)) return (int)cudaErrorInvalidValue;
   const long long items = (long long)p.nchunks * p.ncx;
   if (items > 0x7fffffffLL) return (int)cudaErrorInvalidConfiguration;
   p.nitems = (int)items;
@@ -248,6 +264,7 @@ template <class F, class C, bool FMA> Variant rows2_variant(const char *name) {
   v.tx = G::TX; v.ty = C::RB;
   v.halo_x = 2 * G::VX; v.halo_y = 2;
   v.threads = G::THREADS; v.smem = G::SMEM_BYTES;
+  v.gap_dim = 1;
   v.launch = &launch_rows2<F, C, FMA>;
   return v;
 }
@@ -263,6 +280,7 @@ template <class F, class C, bool FMA, int MARCH = 0> Variant tb2_variant(const c
   v.box_x = G::P0; v.box_y = G::BOX_Y;
   v.halo_x = 2 * G::VX; v.halo_y = 2;
   v.threads = G::THREADS; v.smem = G::SMEM_BYTES;
+  v.gap_dim = MARCH <= 1 ? 0 : -1;   // sweep_tb2, sweep_tb2m
   v.launch = &launch_tb2<F, C, FMA, MARCH>;
   return v;
 }
@@ -277,6 +295,7 @@ template <class F, class C, bool FMA> Variant tma_variant(const char *name) {
   v.box_x = G::SXP; v.box_y = G::SY;
   v.halo_x = G::HX; v.halo_y = G::RY;
   v.threads = G::THREADS; v.smem = G::SMEM_BYTES;
+  v.gap_dim = 0;
   v.launch = &launch_tma<F, C, FMA>;
   return v;
 }

@@ -25,6 +25,8 @@ struct SweepArgs {
   int wlo[3] = {0, 0, 0}, whi[3] = {0, 0, 0};
   double consts[NEPTUNE_RT_MAX_CONSTS] = {};
   int zchunk = 0;        // planes per work item (0: choose)
+  int gap_lo = 0, gap_hi = 0;   // planes [gap_lo, gap_hi) of the marching dimension are left out: the two equally wide
+                                // ranges either side go out as the two chunks of ONE launch (slab boundary planes)
   int sm_count = 148;
   cudaStream_t stream = nullptr;
   const CUtensorMap *tmap = nullptr;  // tensor map of the staged input (TMA variants)
@@ -43,6 +45,7 @@ struct Variant {
   int threads = 0, smem = 0;
   int steps = 1;                // time steps one launch advances (2: temporally blocked)
   bool needs_tmap = true;       // TMA / TB2 kinds: the launch takes a tensor map of the staged input (row kernels use bulk copies)
+  int gap_dim = -1;             // canonical dimension in which the launch honours SweepArgs::gap_lo/gap_hi (-1: it cannot)
   int (*launch)(const SweepArgs &) = nullptr;   // returns a cudaError_t
 };
 

@@ -75,7 +75,7 @@ sweep_rows2(const __grid_constant__ KParams<F> p) {
   // work item -> result rows [yb, ye) of strip x0 .. x0 + TX
   auto geom = [&](int item, int &yb, int &ye, int &x0) {
     const int chunk = item / p.ncx, cx = item - chunk * p.ncx;
-    yb = p.wlo[1] + chunk * p.zchunk;
+    yb = p.wlo[1] + chunk * p.zchunk + (chunk ? p.zgap : 0);
     ye = min(p.whi[1], yb + p.zchunk);
     x0 = (p.cxo + cx) * TX;
   };

@@ -112,7 +112,7 @@ sweep_tb2(const __grid_constant__ KParams<F> p, const __grid_constant__ CUtensor
     const int ncols = p.ncx * p.ncy;
     const int chunk = item / ncols, col = item - chunk * ncols;
     const int cx = col / p.ncy, cy = col - cx * p.ncy;
-    zb = p.wlo[0] + chunk * p.zchunk;
+    zb = p.wlo[0] + chunk * p.zchunk + (chunk ? p.zgap : 0);
     ze = min(p.whi[0], zb + p.zchunk);
     y0 = (p.cyo + cy) * C::TY;
     x0 = (p.cxo + cx) * C::TX;

@@ -714,9 +714,11 @@ bool tb2_eligible(const neptune_rt_stencil *s, neptune_rt_field *a, neptune_rt_f
   return true;
 }
 
-// two_steps: out = apply(apply(in)) in one temporally blocked launch (caller checked tb2_eligible)
+// two_steps: out = apply(apply(in)) in one temporally blocked launch (caller checked tb2_eligible).
+// [g0, g1) non-empty: planes p0..g0 and g1..p1 only (equally wide: the two boundary ranges of a slab),
+// in one launch where the picked kernel can take two ranges, else in two.
 int do_apply(neptune_rt_stencil *s, int n_in, neptune_rt_field *const *in, neptune_rt_field *out, int64_t p0, int64_t p1,
-             cudaStream_t stream, bool two_steps = false) {
+             cudaStream_t stream, bool two_steps = false, int64_t g0 = 0, int64_t g1 = 0) {
   neptune_rt_ctx *c = s->ctx;
   const neptune_rt_stencil_desc &d = s->desc.c;
   if (n_in != d.n_inputs) return set_error(c, NEPTUNE_RT_EINVAL, "neptune_rt_apply: %d inputs given, the apply has %d", n_in, d.n_inputs);
@@ -739,6 +741,10 @@ int do_apply(neptune_rt_stencil *s, int n_in, neptune_rt_field *const *in, neptu
   const int cd0 = 3 - d.rank;
   if (p0 < 0 || p1 > out->ext[cd0] || p0 > p1) return set_error(c, NEPTUNE_RT_EINVAL, "neptune_rt_apply_planes: plane range [%lld, %lld)", (long long)p0, (long long)p1);
   if (p0 == p1 || out->numel() == 0) return NEPTUNE_RT_OK;
+  const bool gap = g1 > g0;
+  if (gap && (g0 <= p0 || g1 >= p1 || g0 - p0 != p1 - g1))
+    return set_error(c, NEPTUNE_RT_EINVAL, "neptune_rt_apply_planes2: [%lld, %lld) does not split [%lld, %lld) into two equally wide ranges",
+                     (long long)g0, (long long)g1, (long long)p0, (long long)p1);
 
   const size_t S = out->elsize();
   a.out = out->dptr;
@@ -794,7 +800,7 @@ int do_apply(neptune_rt_stencil *s, int n_in, neptune_rt_field *const *in, neptu
       // one input, wide box (r01, 512^3 f64): tb2p:128x14 466, tb2m:128x14 427, tb2g:128x14 415, tb2:128x16 409 Gupd/s.
       // The pipelined form pays seven planes of fill and drain per item instead of four: thin launches (the
       // boundary planes of a slab) keep tb2m.
-      const bool deep = p1 - p0 >= 24;
+      const bool deep = (p1 - p0) - (g1 - g0) >= 24 && !gap;
       const char *prefer[] = {n_in > 1 ? two_in : wide ? (deep ? "tb2p:128x14" : "tb2m:128x14") : "tb2:64x16",
                               wide ? "tb2m:128x14" : "tb2:64x16"};
       for (const char *name : prefer) {
@@ -836,6 +842,14 @@ int do_apply(neptune_rt_stencil *s, int n_in, neptune_rt_field *const *in, neptu
       return set_error(c, NEPTUNE_RT_EINVAL, "kernel variant '%s' needs inputs that share the result's box and 16-byte aligned rows", pick->name.c_str());
   }
   if (!pick) return set_error(c, NEPTUNE_RT_EUNSUPPORTED, "no kernel variant '%s' for this body", s->want.c_str());
+  if (gap) {
+    if (pick->gap_dim != cd0) {
+      if (int rc = do_apply(s, n_in, in, out, p0, g0, stream, two_steps)) return rc;
+      return do_apply(s, n_in, in, out, g1, p1, stream, two_steps);
+    }
+    a.gap_lo = (int)g0;
+    a.gap_hi = (int)g1;
+  }
   CUtensorMap tm_staged, tm_pw;   // copies: get_tmap's cache may move its entries on the next call
   if ((pick->kind == neptune::VARIANT_TMA || pick->kind == neptune::VARIANT_TB2) && pick->needs_tmap) {
     const CUtensorMap *tm = nullptr;
@@ -861,6 +875,13 @@ int do_apply(neptune_rt_stencil *s, int n_in, neptune_rt_field *const *in, neptu
 extern "C" int neptune_rt_apply(neptune_rt_stencil *s, int n_in, neptune_rt_field *const *in, neptune_rt_field *out) {
   if (!s || !out) return set_error(s ? s->ctx : nullptr, NEPTUNE_RT_EINVAL, "neptune_rt_apply: NULL argument");
   return do_apply(s, n_in, in, out, 0, out->ext[3 - out->rank], s->ctx->stream);
+}
+
+extern "C" int neptune_rt_apply_planes2(neptune_rt_stencil *s, int n_in, neptune_rt_field *const *in, neptune_rt_field *out,
+                                        int64_t p0, int64_t g0, int64_t g1, int64_t p1, void *stream) {
+  if (!s || !out) return set_error(s ? s->ctx : nullptr, NEPTUNE_RT_EINVAL, "neptune_rt_apply_planes2: NULL argument");
+  if (g1 <= g0) return set_error(s->ctx, NEPTUNE_RT_EINVAL, "neptune_rt_apply_planes2: empty gap [%lld, %lld)", (long long)g0, (long long)g1);
+  return do_apply(s, n_in, in, out, p0, p1, stream ? (cudaStream_t)stream : s->ctx->stream, false, g0, g1);
 }
 
 extern "C" int neptune_rt_apply_planes(neptune_rt_stencil *s, int n_in, neptune_rt_field *const *in, neptune_rt_field *out,
@@ -1104,8 +1125,12 @@ extern "C" int neptune_rt_run_steps(neptune_rt_stencil *s, neptune_rt_field *fa,
     ins[0] = cur;
     // 1. boundary planes of the owned slab, so their exchange can start early
     if (w > 0) {
-      if (up) if (int rc = do_apply(s, d.n_inputs, ins, nxt, own_b, own_b + w, c->stream, two)) return rc;
-      if (down) if (int rc = do_apply(s, d.n_inputs, ins, nxt, own_e - w, own_e, c->stream, two)) return rc;
+      if (up && down && own_b + w < own_e - w) {   // both sides in one launch (two plane ranges)
+        if (int rc = do_apply(s, d.n_inputs, ins, nxt, own_b, own_e, c->stream, two, own_b + w, own_e - w)) return rc;
+      } else {
+        if (up) if (int rc = do_apply(s, d.n_inputs, ins, nxt, own_b, own_b + w, c->stream, two)) return rc;
+        if (down) if (int rc = do_apply(s, d.n_inputs, ins, nxt, own_e - w, own_e, c->stream, two)) return rc;
+      }
     }
     RT_CUDA(c, cudaEventRecord(c->ev_boundary, c->stream));
     RT_CUDA(c, cudaStreamWaitEvent(c->halo_stream, c->ev_boundary, 0));

@@ -98,6 +98,7 @@ def lib() -> C.CDLL:
         "neptune_rt_stencil_variant_name": (C.c_char_p, [vp, i32]),
         "neptune_rt_apply": (i32, [vp, i32, C.POINTER(vp), vp]),
         "neptune_rt_apply_planes": (i32, [vp, i32, C.POINTER(vp), vp, i64, i64, vp]),
+        "neptune_rt_apply_planes2": (i32, [vp, i32, C.POINTER(vp), vp, i64, i64, i64, i64, vp]),
         "neptune_rt_apply_host": (i32, [vp, i32, C.POINTER(vp), C.POINTER(vp), vp, vp, i64]),
         "neptune_rt_run_steps": (i32, [vp, vp, vp, i32, C.POINTER(vp), i64, C.POINTER(vp)]),
         "neptune_rt_slab_partition": (i32, [i64, i32, i32, i64p, i64p]),
@@ -390,6 +391,8 @@ class Stencil:
         arr = (C.c_void_p * len(ins))(*[f.h for f in ins])
         if planes is None:
             rc = self.ctx._L.neptune_rt_apply(self.h, len(ins), arr, out.h)
+        elif len(planes) == 4:   # (p0, g0, g1, p1): planes [p0, g0) and [g1, p1) in one launch
+            rc = self.ctx._L.neptune_rt_apply_planes2(self.h, len(ins), arr, out.h, planes[0], planes[1], planes[2], planes[3], stream or None)
         else:
             rc = self.ctx._L.neptune_rt_apply_planes(self.h, len(ins), arr, out.h, planes[0], planes[1], stream or None)
         self.ctx._check(rc)

@@ -187,6 +187,40 @@ def test_apply_planes_partition(nb, ctx):
         m.destroy()
 
 
+@pytest.mark.parametrize("name,shape", [("heat_star", (30, 32, 64)), ("heat_box_2d9", (40, 1024)), ("heat_star", (33, 512))])
+def test_apply_two_plane_ranges_in_one_launch(nb, ctx, name, shape):
+    """neptune_rt_apply_planes2: the two boundary ranges of a slab as one launch (or two, where the variant
+    cannot) + the interior == one whole sweep, and the gap is left untouched by the first call."""
+    text, _ = H.program(name, list(shape))
+    u, _ = H.inputs(shape, 0, "f64", seed=10)
+    want = H.oracle_entry(text, u, [])
+    n = shape[0]
+    m = nb.Module(text)
+    try:
+        st = m.stencil(ctx, 0)
+        for variant in st.variants():
+            if variant.startswith("tb2"):
+                continue   # two-step kernels take the two ranges in the slab time loop (test_gpu_multi.py)
+            for w in (1, 2, 5):
+                st.set("variant", variant)
+                fin = nb.Field.from_numpy(ctx, u)
+                fout = nb.Field(ctx, np.float64, [0] * len(shape), list(shape))
+                fout.fill(-7.0)
+                st.apply([fin], fout, planes=(0, w, n - w, n))
+                got = fout.download()
+                assert H.bits_equal(got[:w], want[:w]) and H.bits_equal(got[n - w:], want[n - w:]), (variant, w)
+                assert np.all(got[w:n - w] == -7.0), (variant, w, "gap written")
+                st.apply([fin], fout, planes=(w, n - w))
+                assert H.bits_equal(fout.download(), want), (variant, w)
+                fin.free(); fout.free()
+        with pytest.raises(Exception):
+            fin = nb.Field.from_numpy(ctx, u)
+            fout = nb.Field(ctx, np.float64, [0] * len(shape), list(shape))
+            st.apply([fin], fout, planes=(0, 2, n - 3, n))   # ranges of different widths
+    finally:
+        m.destroy()
+
+
 OPDEF_PROGRAM = """
 #loc = #neptune_ir.location<"cell">
 #b   = #neptune_ir.bounds<lb = [0, 0], ub = [48, 64]>
