@@ -1119,21 +1119,33 @@ extern "C" int neptune_rt_run_steps(neptune_rt_stencil *s, neptune_rt_field *fa,
       if (int rc = neptune_rt_halo_exchange(c, extra[k], own_b, own_e, ghost, c->halo_stream)) return rc;
   RT_CUDA(c, cudaEventRecord(c->ev_halo, c->halo_stream));
   RT_CUDA(c, cudaStreamWaitEvent(c->stream, c->ev_halo, 0));
+  const char *sb_env = std::getenv("NEPTUNE_RT_SLAB_BOUNDARY_STREAM");
+  const bool side_boundary = sb_env && sb_env[0] == '1';
   for (int64_t t = 0; t < nsteps;) {
     const bool two = fuse2 && t + 2 <= nsteps;
     const int64_t w = two ? 2 * radius : radius;  // planes computed first and exchanged
     ins[0] = cur;
     // 1. boundary planes of the owned slab, so their exchange can start early
+    // NEPTUNE_RT_SLAB_BOUNDARY_STREAM=1 (experimental): the boundary launch goes to the high-priority
+    // stream, beside the interior (they write disjoint planes) instead of ahead of it
+    cudaStream_t bstream = c->stream;
+    if (side_boundary) {
+      RT_CUDA(c, cudaEventRecord(c->ev_boundary, c->stream));
+      RT_CUDA(c, cudaStreamWaitEvent(c->halo_stream, c->ev_boundary, 0));
+      bstream = c->halo_stream;
+    }
     if (w > 0) {
       if (up && down && own_b + w < own_e - w) {   // both sides in one launch (two plane ranges)
-        if (int rc = do_apply(s, d.n_inputs, ins, nxt, own_b, own_e, c->stream, two, own_b + w, own_e - w)) return rc;
+        if (int rc = do_apply(s, d.n_inputs, ins, nxt, own_b, own_e, bstream, two, own_b + w, own_e - w)) return rc;
       } else {
-        if (up) if (int rc = do_apply(s, d.n_inputs, ins, nxt, own_b, own_b + w, c->stream, two)) return rc;
-        if (down) if (int rc = do_apply(s, d.n_inputs, ins, nxt, own_e - w, own_e, c->stream, two)) return rc;
+        if (up) if (int rc = do_apply(s, d.n_inputs, ins, nxt, own_b, own_b + w, bstream, two)) return rc;
+        if (down) if (int rc = do_apply(s, d.n_inputs, ins, nxt, own_e - w, own_e, bstream, two)) return rc;
       }
     }
-    RT_CUDA(c, cudaEventRecord(c->ev_boundary, c->stream));
-    RT_CUDA(c, cudaStreamWaitEvent(c->halo_stream, c->ev_boundary, 0));
+    if (!side_boundary) {
+      RT_CUDA(c, cudaEventRecord(c->ev_boundary, c->stream));
+      RT_CUDA(c, cudaStreamWaitEvent(c->halo_stream, c->ev_boundary, 0));
+    }
     // 2. halo exchange of the new state on the high-priority stream, concurrent with 3.
     if (int rc = neptune_rt_halo_exchange(c, nxt, own_b, own_e, w, c->halo_stream)) return rc;
     RT_CUDA(c, cudaEventRecord(c->ev_halo, c->halo_stream));
