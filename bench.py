@@ -40,6 +40,8 @@ WORKLOADS = {
     "c1": ("heat_star", [4096, 4096], "f64", 0.2, 16, "2D 5-pt fp64 heat step, 4096^2 (BASELINE configs[0])"),
     "c5": ("jacobi_star", [768, 768, 768], "f64", None, 24, "3D 7-pt Jacobi with rhs, 768^3 f64 (BASELINE configs[4], 1 GPU)"),
     "c5f32": ("jacobi_star", [768, 768, 768], "f32", None, 12, "3D 7-pt Jacobi with rhs, 768^3 f32 (BASELINE configs[4], 1 GPU)"),
+    "c5g": ("jacobi_star", [96, 768, 768], "f64", None, 24, "3D 7-pt Jacobi with rhs, fp64, 96x768x768 per GPU = 768^3 over 8 GPUs (BASELINE configs[4] as worded)"),
+    "c5gf32": ("jacobi_star", [96, 768, 768], "f32", None, 12, "3D 7-pt Jacobi with rhs, fp32, 96x768x768 per GPU = 768^3 over 8 GPUs (BASELINE configs[4] as worded)"),
     "c4": ("varcoef27", [128, 1024, 1024], "f64", None, 232, "3D 27-pt variable-coefficient fp64 (27 coefficient fields), 128x1024x1024 per GPU = 1024^3 over 8 GPUs (BASELINE configs[3])"),
     "tiny": ("heat_star", [64, 64, 128], "f64", 0.1, 16, "3D 7-pt fp64 heat step, 64x64x128 (self-test)"),
 }
@@ -59,6 +61,68 @@ def program_text(name, shape):
     raise KeyError(kind)
 
 
+def program_for(kind, shape, ty, alpha, h2, lb=None):
+    """The workload's NeptuneIR text at another extent with the SAME constants (band cones, local slab programs)."""
+    from neptune_pde_solver_b200 import mlir_builders as mb
+    if kind == "heat_star":
+        return mb.heat_star(shape, alpha, ty, lb)
+    if kind == "heat_box_2d9":
+        return mb.heat_box_2d9(shape, alpha, ty, lb)
+    if kind == "jacobi_star":
+        return mb.jacobi_star(shape, h2, ty, lb)
+    if kind == "varcoef27":
+        return mb.varcoef(shape, mb.box_offsets(3), ty, lb)
+    raise KeyError(kind)
+
+
+PARITY_STEPS = 4
+
+
+def band_parity_check(kind, ty, alpha, h2, world, rank, own_rows, u_local, extra_local, run_fn, gather_fn):
+    """Bitwise parity inside the benchmark run, on the ACTUAL configuration (kernel variant, slab decomposition,
+    ghost depth, NCCL exchange): 4 steps from the benchmark's initial state, then an 8-plane band that straddles
+    every slab boundary (N = 1: the middle of the domain) is compared with the oracle run on the band's dependency
+    cone (16 planes x a corner block that includes two real faces; the cone's own cut faces cannot reach the band
+    in 4 steps).  The oracle is the checker here, never the thing measured."""
+    rank_nd = u_local.ndim
+    cut = (slice(0, min(96, u_local.shape[1])), slice(0, min(160, u_local.shape[2]))) if rank_nd == 3 else (slice(0, min(4096, u_local.shape[1])),)
+    ob, oe = own_rows
+    S = PARITY_STEPS
+    res_local = run_fn(S)                       # numpy array of the local box after S steps
+    if world == 1:
+        mid = (ob + oe) // 2
+        packs = [{"init": [np.ascontiguousarray(a[(slice(mid - 2 * S, mid + 2 * S),) + cut]) for a in [u_local] + extra_local],
+                  "res": np.ascontiguousarray(res_local[(slice(mid - S, mid + S),) + cut]), "where": "planes [%d, %d) of the single domain" % (mid - S, mid + S)}]
+    else:
+        mine = {"top_init": [np.ascontiguousarray(a[(slice(ob, ob + 2 * S),) + cut]) for a in [u_local] + extra_local],
+                "bot_init": [np.ascontiguousarray(a[(slice(oe - 2 * S, oe),) + cut]) for a in [u_local] + extra_local],
+                "top_res": np.ascontiguousarray(res_local[(slice(ob, ob + S),) + cut]),
+                "bot_res": np.ascontiguousarray(res_local[(slice(oe - S, oe),) + cut])}
+        parts = gather_fn(mine)
+        if rank != 0:
+            return None
+        packs = []
+        for r in range(world - 1):
+            packs.append({"init": [np.concatenate([a, b], axis=0) for a, b in zip(parts[r]["bot_init"], parts[r + 1]["top_init"])],
+                          "res": np.concatenate([parts[r]["bot_res"], parts[r + 1]["top_res"]], axis=0),
+                          "where": "last %d planes of rank %d + first %d planes of rank %d" % (S, r, S, r + 1)})
+    from oracle import mlir_subset as ms, numpy_lowering as onp
+    ok, bands = True, []
+    for pk in packs:
+        cone = pk["init"][0]
+        text = program_for(kind, list(cone.shape), ty, alpha, h2)
+        want = onp.run_steps(ms.parse(text), cone, pk["init"][1:], S)
+        inner = (slice(S, 3 * S),) + tuple(slice(0, n - S) for n in cone.shape[1:])
+        trim = (slice(None),) + tuple(slice(0, n - S) for n in cone.shape[1:])
+        a, b = pk["res"][trim], want[inner]
+        view = np.uint64 if a.dtype == np.float64 else np.uint32
+        eq = bool(a.shape == b.shape and np.array_equal(a.view(view), b.view(view)))
+        ok &= eq
+        bands.append({"band": pk["where"], "points": int(a.size), "bits_equal": eq})
+    return {"bits_equal": ok, "steps": S, "bands": bands,
+            "oracle": "oracle/numpy_lowering.py on each band's 16-plane dependency cone (restatement of DataflowLowering.cpp:258-448)"}
+
+
 def synth(shape, ty, seed):
     """u0 = product of sines + 0.25 U(-1,1), generated plane-block-wise."""
     dt = np.float64 if ty == "f64" else np.float32
@@ -73,6 +137,16 @@ def synth(shape, ty, seed):
             t = np.multiply.outer(t, a)
         u[p:q] = (t + 0.25 * rng.uniform(-1, 1, size=t.shape)).astype(dt)
     return u
+
+
+def kernel_digest():
+    """Digest of the CUDA kernel sources: stamps ncu-derived numbers so that they go stale loudly."""
+    import glob
+    import hashlib
+    h = hashlib.sha256()
+    for f in sorted(glob.glob(os.path.join(ROOT, "neptune_pde_solver_b200", "csrc", "kernels", "*.cuh"))):
+        h.update(open(f, "rb").read())
+    return h.hexdigest()[:16]
 
 
 def interior_points(shape):
@@ -193,7 +267,10 @@ def run_reference(args):
         "impl": "reference", "metric": METRIC, "value": gups, "unit": UNIT, "n_gpus": args.gpus,
         "steps": n, "warmup": w, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": WORKLOADS[args.workload][2], "data": "synthetic",
-        "config": {"workload": WORKLOADS[args.workload][5], "grid": shape, "points_per_step": interior_points(shape)},
+        "config": {"workload": WORKLOADS[args.workload][5], "grid_per_gpu": list(shape), "global_grid": list(shape),
+                   "decomposition": "single domain on the host (the reference has no decomposition); at --gpus N > 1 this arm still "
+                                    "sweeps ONE %s domain on one core, so the N-GPU ratio compares an N-GPU job with a 1-core job" % "x".join(map(str, shape)),
+                   "points_per_step": interior_points(shape), "kernel_variant": "cpu scalar loop nest", "fma": False},
         "cpu_baseline": {"value": gups, "unit": UNIT, "cores": cores, "kind": "port",
                          "sample": "%d full sweeps of the workload grid, gcc -O2 -ffp-contract=off scalar, "
                                    "incl. per-sweep malloc + copy-through + store copy "
@@ -239,17 +316,20 @@ def run_b200(args):
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
 
-    kind, shape1, ty, _, bytes_per_update, descr = WORKLOADS[args.workload]
+    kind, shape1, ty, alpha, bytes_per_update, descr = WORKLOADS[args.workload]
     dt = np.float64 if ty == "f64" else np.float32
     # weak scaling: global grid = (N * n0) x n1 x n2, dim 0 sharded
     gshape = [shape1[0] * world] + list(shape1[1:])
+    h2 = 1.0 / (max(gshape) ** 2)
     gtext, n_extra = program_text(args.workload, gshape)
     ctx = nb.Context(local)
     gdesc = nb.Module(gtext).apply_desc(0)
     if world > 1:
-        # two ghost planes per neighbour side where the body has a temporally blocked kernel: one
-        # exchange of two planes per fused pair of steps (neptune_rt_stencil_set_slab)
-        slab = Slab(gdesc, world, rank, halo=2 * gdesc.radius0() if kind in ("heat_star", "jacobi_star", "heat_box_2d9") and args.tblock != 1 else None)
+        # ghost planes per neighbour side: 2 * radius lets a launch fuse two steps (one exchange per fused pair);
+        # deeper ghosts (--ghost) exchange once every ghost / (2 * radius) launches (neptune_rt_stencil_set_slab)
+        fusable = kind in ("heat_star", "jacobi_star", "heat_box_2d9") and args.tblock != 1
+        halo = args.ghost if args.ghost > 0 else (max(2, args.tblock) * gdesc.radius0() if fusable else None)
+        slab = Slab(gdesc, world, rank, halo=halo)
         lshape = list(slab.local_shape(gshape))
         from neptune_pde_solver_b200 import mlir_builders as mb  # local program: same body, local bounds
         ldesc = slab.local
@@ -280,7 +360,7 @@ def run_b200(args):
     fb = nb.Field(ctx, dt, lb, ub)
     fa.upload(u)
     fb.upload(u)   # both ping-pong buffers start with a valid boundary shell
-    extra = []
+    extra, extra_host = [], []
     for k in range(n_extra):
         f = nb.Field(ctx, dt, lb, ub)
         c = synth(lshape, ty, 20260500 + k + 100 * rank)
@@ -289,6 +369,8 @@ def run_b200(args):
         f.upload(c)
         ctx.sync()
         extra.append(f)
+        if not args.no_parity:
+            extra_host.append(c)
 
     def barrier():
         ctx.sync()
@@ -296,7 +378,43 @@ def run_b200(args):
             dist.barrier()
         torch.cuda.synchronize()
 
-    # ---- device-resident timing: W warm-up steps, then exactly K steps ---------------------------
+    # ---- parity, in this run, on this configuration (before anything is timed) -------------------
+    parity = None
+    if not args.no_parity:
+        if world > 1:
+            ob, oe = slab.own_rows
+            # the initial ghost planes of a rank hold its own synthetic data; the first exchange replaces them
+            # with the neighbours' owned planes, so the global initial state is the concatenation of the owned parts
+        else:
+            ob, oe = 0, lshape[0]
+
+        def run_fn(nsteps):
+            r = stencil.run_steps(fa, fb, extra, nsteps)
+            return r.download()
+
+        def gather_fn(mine):
+            parts = [None] * world
+            dist.all_gather_object(parts, mine)
+            return parts
+
+        parity = band_parity_check(kind, ty, alpha, h2, world, rank, (ob, oe), u, extra_host, run_fn, gather_fn)
+        if world > 1:
+            flag = [parity["bits_equal"] if rank == 0 else None]
+            dist.broadcast_object_list(flag, src=0)
+            ok = flag[0]
+        else:
+            ok = parity["bits_equal"]
+        if rank == 0:
+            parity["kernel_variant"] = stencil.variant()
+        if not ok:
+            if rank == 0:
+                print(json.dumps({"error": "parity check failed", "parity_check": parity}), flush=True)
+            raise SystemExit(3)
+        fa.upload(u)
+        fb.upload(u)
+        del extra_host
+
+    # ---- device-resident timing: W warm-up steps, then exactly K steps, REPS times; median ---------
     cur = stencil.run_steps(fa, fb, extra, args.warmup)
     other = fb if cur is fa else fa
     barrier()
@@ -305,28 +423,49 @@ def run_b200(args):
         sampler.start()
         time.sleep(0.25)
     barrier()
-    n0 = ctx.launch_count()
     t_wall0 = time.time()
-    ctx.timer_start()
-    cur = stencil.run_steps(cur, other, extra, args.steps)
-    ms = ctx.timer_stop()
-    other = fb if cur is fa else fa
-    barrier()
+    rep_ms, launches = [], 0
+    for rep in range(max(1, args.reps)):
+        barrier()
+        n0 = ctx.launch_count()
+        ctx.timer_start()
+        cur = stencil.run_steps(cur, other, extra, args.steps)
+        ms_rep = ctx.timer_stop()
+        other = fb if cur is fa else fa
+        barrier()
+        launches = ctx.launch_count() - n0
+        if world > 1:
+            t = torch.tensor([ms_rep], dtype=torch.float64, device="cuda")
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)      # a repetition takes as long as its slowest rank
+            ms_rep = float(t[0])
+        rep_ms.append(ms_rep)
     t_wall1 = time.time()
-    launches = ctx.launch_count() - n0
     clocks = sampler.stop(t_wall0, t_wall1) if rank == 0 else None
+    ms = float(np.median(rep_ms))
     if world > 1:
-        t = torch.tensor([ms, float(own_points), float(launches)], dtype=torch.float64, device="cuda")
-        tmax = t.clone()
-        dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
-        tsum = t.clone()
-        dist.all_reduce(tsum, op=dist.ReduceOp.SUM)
-        ms_max, total_points, launches_all = float(tmax[0]), float(tsum[1]), int(tsum[2])
+        t = torch.tensor([float(own_points), float(launches)], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        ms_max, total_points, launches_all = ms, float(t[0]), int(t[1])
     else:
         ms_max, total_points, launches_all = ms, float(own_points), launches
     ms_per_step = ms_max / args.steps
     value = total_points / (ms_per_step * 1e-3) / 1e9
     variant = stencil.variant()
+
+    # ---- timeline of the slab time loop (one rank with two neighbours where there is one) ----------
+    slab_trace = None
+    if world > 1 and args.trace:
+        ctx.slab_trace(True)
+        cur = stencil.run_steps(cur, other, extra, args.steps)
+        other = fb if cur is fa else fa
+        rows = ctx.slab_trace_read()
+        ctx.slab_trace(False)
+        allrows = [None] * world
+        dist.all_gather_object(allrows, rows)
+        pick = 1 if world > 2 else 0
+        slab_trace = {"rank": pick, "unit": "ms since the first group began",
+                      "columns": ["kind (10*steps + exchanged)", "begin", "boundary_done", "exchange_done", "interior_done"],
+                      "groups": [[g[0]] + [round(x, 4) for x in g[1:]] for g in allrows[pick][:12]]}
 
     # ---- roofline of the dominant kernel: whole-box sweep launches timed with CUDA events on the
     # launching stream (at N=1 the timed region above IS K such launches, one per step) ------------
@@ -351,7 +490,7 @@ def run_b200(args):
             stencil.set("tblock", args.tblock)
     else:
         steps_per_launch = 2.0 if variant.startswith("tb2") else 1.0
-        kernel_ms = ms / (args.steps / steps_per_launch)    # boundary + interior launches and any exposed halo wait
+        kernel_ms = ms / (args.steps / steps_per_launch)    # per launch group: sweep launches and any exposed halo wait
     box_points = own_points
     peaks = {}
     try:
@@ -361,10 +500,19 @@ def run_b200(args):
     peak = float(peaks.get("hbm_gbs", 6650.0))
     peak_kind = "measured (MEASURED_PEAKS.json hbm_gbs)" if "hbm_gbs" in peaks else "fallback 6650 GB/s (B200_PROFILING.md)"
     achieved = box_points * bytes_per_update * steps_per_launch / (kernel_ms * 1e-3) / 1e9
-    traffic = args.traffic
+    traffic, traffic_note = args.traffic, None
     if traffic is None and world == 1:
-        try:   # per-launch DRAM bytes of this kernel from the committed ncu --set full capture
-            traffic = json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get(args.workload, {}).get(variant)
+        try:   # per-launch DRAM bytes of this kernel from the committed ncu --set full capture, valid only for the kernel
+            # sources it was captured from (entries are stamped with a digest of csrc/kernels/)
+            ent = json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get(args.workload, {}).get(variant)
+            if isinstance(ent, dict):
+                if ent.get("digest") == kernel_digest():
+                    traffic = ent.get("bytes")
+                else:
+                    traffic_note = "profiles/traffic.json entry for %s was captured from other kernel sources (digest %s, now %s): not reported" % (
+                        variant, ent.get("digest"), kernel_digest())
+            elif ent is not None:
+                traffic_note = "profiles/traffic.json entry for %s carries no source digest: not reported" % variant
         except (OSError, ValueError):
             traffic = None
     roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
@@ -373,6 +521,8 @@ def run_b200(args):
                 "algorithmic_bytes_per_launch": box_points * bytes_per_update * steps_per_launch,
                 "steps_per_launch": steps_per_launch,
                 "bytes_per_update": bytes_per_update}
+    if traffic_note:
+        roofline["traffic_note"] = traffic_note
     if steps_per_launch > 1:
         roofline["note"] = ("temporally blocked kernel: two time steps per launch, so algorithmic bytes (16 B per point-update) "
                             "exceed the DRAM bytes moved (see traffic); frac > 1 of the copy peak is possible by construction")
@@ -380,23 +530,14 @@ def run_b200(args):
         single["frac"] = single["achieved"] / peak
         roofline["single_step_kernel"] = single
 
-    # ---- e2e: the reference-facing entry call on HOST memrefs, copies inside the timed region -----
+    # ---- e2e: host buffers in, host buffers out, copies inside the timed region every step ---------
+    # N = 1: the reference-facing entry call `@entry(out, in)` on pinned host memrefs (neptune_b200_run_host).
+    # N > 1: every rank uploads its local box, runs ONE slab-mode step (halo exchange included) and downloads it;
+    #        the single-GPU entry has no decomposition, so the multi-GPU public API (Slab + run_steps) is used.
     e2e, e_launches = None, 0
     field_bytes = int(np.prod(lshape)) * np.dtype(dt).itemsize
     if args.e2e_steps > 0:
-        from neptune_pde_solver_b200 import mlir_builders as mb
-        if world > 1:
-            ltext = {"heat_star": lambda: mb.heat_star(lshape, WORKLOADS[args.workload][3], ty, lb),
-                     "heat_box_2d9": lambda: mb.heat_box_2d9(lshape, WORKLOADS[args.workload][3], ty, lb),
-                     "jacobi_star": lambda: mb.jacobi_star(lshape, 1.0 / (max(gshape) ** 2), ty, lb),
-                     "varcoef27": lambda: mb.varcoef(lshape, mb.box_offsets(3), ty, lb)}[kind]()
-            emod = nb.Module(ltext)
-        else:
-            emod = mod
-        if args.variant:
-            emod.stencil(ctx, 0).set("variant", args.variant)
-        keep = []
-        hargs = []
+        keep, hargs = [], []
         for k in range(2 + n_extra):
             t, a = pinned_like(lshape, dt)
             keep.append(t)
@@ -405,14 +546,34 @@ def run_b200(args):
         for k in range(n_extra):
             hargs[2 + k][...] = synth(lshape, ty, 20260500 + k + 100 * rank)
         e_steps = max(1, min(args.steps, args.e2e_steps))
+        if world == 1:
+            emod = mod
+            if args.variant:
+                emod.stencil(ctx, 0).set("variant", args.variant)
+
+            def e2e_step():
+                emod.run(ctx, "@entry", hargs)          # upload inputs, sweep, download result, sync
+                hargs[0], hargs[1] = hargs[1], hargs[0]  # the host time loop's swap
+            api = ("neptune_b200_run_host(@entry(out, in)) on pinned host memrefs, one sweep per call; upload | sweep | download "
+                   "pipelined over dim-0 plane chunks (neptune_rt_apply_host)")
+        else:
+            def e2e_step():
+                fa.upload_planes(hargs[1], 0, lshape[0])
+                for k in range(n_extra):
+                    extra[k].upload_planes(hargs[2 + k], 0, lshape[0])
+                r = stencil.run_steps(fa, fb, extra, 1)  # ghost exchange + boundary / interior sweep of this rank's slab
+                r.download_planes(hargs[0], 0, lshape[0])
+                ctx.sync()
+                hargs[0], hargs[1] = hargs[1], hargs[0]
+            api = ("per rank: neptune_rt_field_upload(local box, pinned) + neptune_rt_run_steps(1 step, slab mode, NCCL halo exchange) + "
+                   "neptune_rt_field_download; not pipelined")
         for _ in range(2):
-            emod.run(ctx, "@entry", hargs)
+            e2e_step()
         barrier()
         l0 = ctx.launch_count()
         t0 = time.perf_counter()
         for _ in range(e_steps):
-            emod.run(ctx, "@entry", hargs)          # upload inputs, sweep, download result, sync
-            hargs[0], hargs[1] = hargs[1], hargs[0]  # the host time loop's swap
+            e2e_step()
         barrier()
         e_sec = time.perf_counter() - t0
         e_launches = ctx.launch_count() - l0
@@ -421,10 +582,32 @@ def run_b200(args):
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
             e_sec = float(t[0])
         e_value = total_points / (e_sec / e_steps) / 1e9
-        field_bytes = int(np.prod(lshape)) * np.dtype(dt).itemsize
         e2e = {"value": e_value, "unit": UNIT, "h2d_bytes_per_step": field_bytes * (1 + n_extra) * world,
-               "d2h_bytes_per_step": field_bytes * world, "steps": e_steps, "ms_per_step": e_sec / e_steps * 1e3,
-               "api": "neptune_b200_run_host(@entry(out, in)) on pinned host memrefs, one sweep per call; upload | sweep | download pipelined over dim-0 plane chunks (neptune_rt_apply_host)"}
+               "d2h_bytes_per_step": field_bytes * world, "steps": e_steps, "ms_per_step": e_sec / e_steps * 1e3, "api": api}
+        if args.link_probe:
+            # what the host links give when every rank copies at once: bare cudaMemcpyAsync H2D and D2H of one field each,
+            # concurrently on two streams (the ceiling of any host-buffer path on this box)
+            import torch as _t
+            dev = _t.empty(int(np.prod(lshape)), dtype=_t.float64 if dt == np.float64 else _t.float32, device="cuda")
+            dev2 = _t.empty_like(dev)
+            s1, s2 = _t.cuda.Stream(), _t.cuda.Stream()
+            barrier()
+            t0 = time.perf_counter()
+            for _ in range(3):
+                with _t.cuda.stream(s1):
+                    dev.copy_(keep[0].view(-1), non_blocking=True)
+                with _t.cuda.stream(s2):
+                    keep[1].view(-1).copy_(dev2, non_blocking=True)
+            s1.synchronize(); s2.synchronize()
+            barrier()
+            sec = (time.perf_counter() - t0) / 3
+            if world > 1:
+                t = _t.tensor([sec], dtype=_t.float64, device="cuda")
+                dist.all_reduce(t, op=dist.ReduceOp.MAX)
+                sec = float(t[0])
+            e2e["host_link_probe"] = {"GBps_each_way_per_rank": field_bytes / sec / 1e9, "ranks_at_once": world,
+                                      "note": "bare pinned cudaMemcpyAsync H2D + D2H of one field each, concurrently, all ranks at once"}
+            del dev, dev2
 
     # ---- CPU baseline (rank 0, N=1 only): bounded sample of the same workload --------------------
     cpu = None
@@ -449,15 +632,21 @@ def run_b200(args):
             "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": ty, "data": "synthetic",
             "config": {"workload": descr, "grid_per_gpu": list(shape1), "global_grid": gshape,
-                       "decomposition": ("dim-0 slabs, %d ghost plane(s) per neighbour side, one NCCL send/recv exchange per %s overlapped with the interior sweep"
-                                         % (slab.halo, "fused pair of steps" if variant.startswith("tb2") else "step")) if world > 1 else "single domain",
+                       "decomposition": ("dim-0 slabs, %d ghost plane(s) per neighbour side, %d step(s) per launch, one NCCL send/recv exchange of %d plane(s) every %d step(s), "
+                                         "overlapped with the interior sweep of the launch that precedes it"
+                                         % (slab.halo, 2 if variant.startswith("tb2") else 1, slab.halo, max(1, slab.halo // max(1, gdesc.radius0())))) if world > 1 else "single domain",
                        "points_per_step": int(total_points), "kernel_variant": variant,
+                       "timing": "median of %d repetitions of exactly %d steps each, CUDA events on the sweep stream, max over ranks per repetition" % (len(rep_ms), args.steps),
+                       "rep_ms": [round(x, 4) for x in rep_ms], "rep_spread": (max(rep_ms) - min(rep_ms)) / ms if ms > 0 else None,
+                       "parity_check": parity,
                        "l2": "inputs larger than L2 (%.2f GB per field vs 126 MB L2); no flush needed" % (field_bytes / 1e9),
-                       "fma": False, "parity": "bit-exact vs oracle (tests/test_gpu_parity.py)"},
+                       "fma": False},
             "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e,
             "gpu_launches": int(launches_all), "e2e_gpu_launches": int(e_launches), "clocks": clocks,
             "achieved_GBps_step": total_points * bytes_per_update / (ms_per_step * 1e-3) / 1e9 / world,
         }
+        if slab_trace:
+            line["slab_trace"] = slab_trace
         print(json.dumps(line), flush=True)
     for f in [fa, fb] + extra:
         f.free()
@@ -476,7 +665,12 @@ def main():
     ap.add_argument("--workload", default="c3", choices=sorted(WORKLOADS))
     ap.add_argument("--variant", default="")
     ap.add_argument("--zchunk", default="")
-    ap.add_argument("--tblock", type=int, default=0, help="time steps fused per launch (1 or 2; 0 = library default)")
+    ap.add_argument("--tblock", type=int, default=0, help="temporal block depth: 1 or 2 steps per launch (0 = library default); 4 / 8 = two steps per launch and, in slab mode, one exchange of tblock * radius ghost planes per tblock steps")
+    ap.add_argument("--ghost", type=int, default=0, help="ghost planes per neighbour side in slab mode (0 = 2 * radius where two steps fuse, else radius)")
+    ap.add_argument("--reps", type=int, default=5, help="repetitions of the K-step timed region; the median is reported")
+    ap.add_argument("--no-parity", action="store_true", help="skip the in-run bitwise parity check against the oracle")
+    ap.add_argument("--trace", action="store_true", help="N > 1: add per-launch-group timestamps of the slab time loop")
+    ap.add_argument("--link-probe", action="store_true", help="add a bare pinned-memcpy H2D+D2H measurement (all ranks at once) to e2e")
     ap.add_argument("--e2e-steps", type=int, default=10)
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
     ap.add_argument("--no-cpu", action="store_true")

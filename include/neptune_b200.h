@@ -26,8 +26,13 @@ extern "C" {
 typedef struct neptune_b200_module neptune_b200_module;
 
 /* Parse + verify + recognise. `pipeline` must be "neptuneir-to-b200" (options may follow in
- * braces: "neptuneir-to-b200{fma=true}").  On failure returns NEPTUNE_RT_EINVAL /
- * NEPTUNE_RT_EUNSUPPORTED and writes the diagnostic into err (NUL-terminated, truncated). */
+ * braces: "neptuneir-to-b200{fma=true}").  Every function of the module is lowered on its own: one that
+ * holds something outside the hot path (neptune_ir.time_advance, a body with control flow, ...) or breaks a
+ * verifier rule is kept as a rejected function with its diagnostic (neptune_b200_function_diagnostic) and the
+ * others — the operator definitions a time_advance refers to, for one — are still lowered, so the reference's
+ * own fixtures (test/smoke_tests/smoke_time_advance.mlir) compile as far as they are on the path.  When NO
+ * function lowers the call fails like a failed conversion: NEPTUNE_RT_EINVAL / NEPTUNE_RT_EUNSUPPORTED with the
+ * first diagnostic in err (NUL-terminated, truncated). */
 int neptune_b200_compile(const char *mlir_text, const char *pipeline, neptune_b200_module **module,
                          char *err, size_t err_len);
 int neptune_b200_module_destroy(neptune_b200_module *module);
@@ -46,6 +51,10 @@ const char *neptune_b200_function_plan(neptune_b200_module *module, const char *
 int neptune_b200_function_arg_count(neptune_b200_module *module, const char *function);
 int64_t neptune_b200_function_arg_numel(neptune_b200_module *module, const char *function, int arg);
 
+/* Every function of the module, in program order, and why one was not lowered (NULL: it was). Borrowed pointers. */
+int neptune_b200_function_count(neptune_b200_module *module);
+const char *neptune_b200_function_name(neptune_b200_module *module, int index);
+const char *neptune_b200_function_diagnostic(neptune_b200_module *module, const char *function);
 /* Message of the last failed call on this module. Borrowed pointer. */
 const char *neptune_b200_last_error(neptune_b200_module *module);
 /* The runtime stencil apply `index` runs with on `ctx` (created on first use), for tuning through
@@ -59,7 +68,9 @@ const char *neptune_b200_apply_cuda_source(neptune_b200_module *module, int inde
 /* Execute `function` the way the reference's compiled entry would be called by a host driver
  * (test/smoke_tests/smoke_apply.sh:39-80): args[i] are host pointers to the contiguous row-major
  * memref arguments; `wrap` aliases them, `store`/`unwrap` make results visible in them.
- * Uploads, runs every apply on the GPU, downloads what was written. */
+ * Uploads, runs every apply on the GPU, downloads what was written.
+ * An operator definition (linear_opdef / nonlinear_opdef, which StructureLowering.cpp:31-140 turns into a
+ * func.func) is called with its temp operands' buffers followed by ONE more buffer that receives the result. */
 int neptune_b200_run_host(neptune_b200_module *module, neptune_rt_ctx *ctx, const char *function,
                           int n_args, void *const *args);
 /* Scalar values (results of `neptune_ir.reduce`, NeptuneIROps.td:272-299) the function returned in

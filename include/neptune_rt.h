@@ -210,8 +210,11 @@ int neptune_rt_slab_localize(const neptune_rt_stencil_desc *global_desc, int nra
 /* Tells a stencil created from a localized descriptor how its box sits in the global domain:
  * `ghost` planes on every dim-0 side that has a neighbour (the `halo` given to slab_localize) and
  * the GLOBAL apply bounds along dim 0. With ghost >= 2*radius neptune_rt_run_steps fuses two time
- * steps per launch and exchanges 2*radius planes every two steps; without this call it assumes
- * ghost = radius and runs one step per launch. */
+ * steps per launch; with G ghost planes it exchanges G planes once every G / (radius * steps per launch)
+ * launches, the launches in between also computing the ghost planes that stay valid (deep halos: fewer
+ * thin boundary launches and exchanges for a few redundant planes). Without this call it assumes
+ * ghost = radius and runs one step per launch. Decisions that depend on rank-local facts (slab thickness,
+ * alignment) are agreed by all ranks with one small ncclAllReduce per (fields, settings). */
 int neptune_rt_stencil_set_slab(neptune_rt_stencil *stencil, int64_t ghost, int64_t global_lb0,
                                 int64_t global_ub0);
 /* 128-byte NCCL unique id (rank 0 creates it; the host harness broadcasts it). */
@@ -222,13 +225,36 @@ int neptune_rt_comm_init(neptune_rt_ctx *ctx, const void *id128, int nranks, int
 int neptune_rt_halo_exchange(neptune_rt_ctx *ctx, neptune_rt_field *field, int64_t own_begin,
                              int64_t own_end, int64_t width, void *stream);
 
+/* Timeline of the slab time loop, for measuring what the exchange costs: after neptune_rt_slab_trace(ctx, 1) the
+ * next neptune_rt_run_steps records four CUDA events per launch group; neptune_rt_slab_trace_read returns the
+ * number of groups and writes, per group, milliseconds since the first group began: [0] group begins, [1] boundary
+ * planes done, [2] halo exchange done, [3] interior done; kinds[g] = 10 * steps advanced + (1 if it exchanged). */
+int neptune_rt_slab_trace(neptune_rt_ctx *ctx, int enable);
+int neptune_rt_slab_trace_read(neptune_rt_ctx *ctx, double *ms4, int capacity_groups, int *kinds);
+
 /* ---- memref-level entry points (what MLIR-generated code calls) -------------------------- */
-/* Host-buffer form of one sweep, the drop-in for the loop nest the reference emits: uploads the
- * inputs, sweeps, downloads into `out_host`. Buffers are contiguous row-major boxes matching the
- * descriptor's bounds. Uses a lazily created default ctx and aborts on failure, mirroring
- * the reference shim's behaviour (NeptunePETScRuntime.cpp:15-30, 91-98). */
+/* MLIR's memref descriptor as the LLVM lowering lays it out, same field order as the reference's
+ * NeptuneMemRef1D / NeptuneMemRef2D (include/Runtime/PETSc/NeptunePETScRuntime.h:22-42). */
+typedef struct neptune_rt_memref_1d { void *allocated; void *aligned; int64_t offset; int64_t sizes[1]; int64_t strides[1]; } neptune_rt_memref_1d;
+typedef struct neptune_rt_memref_2d { void *allocated; void *aligned; int64_t offset; int64_t sizes[2]; int64_t strides[2]; } neptune_rt_memref_2d;
+typedef struct neptune_rt_memref_3d { void *allocated; void *aligned; int64_t offset; int64_t sizes[3]; int64_t strides[3]; } neptune_rt_memref_3d;
+/* One sweep on host memrefs — the drop-in for the loop nest the reference emits for an apply
+ * (lib/Passes/DataflowLowering.cpp:258-448): `in` points to n_in descriptors (generated code builds the array on
+ * its stack), `out` to the result's. Element (i0, i1, ...) is aligned[offset + sum i_k * strides[k]]; sizes must
+ * equal the apply's operand / result types and strides must be the identity (row-major contiguous) layout —
+ * anything else aborts with a message naming the dimension (a silent wrong answer is worse). The stencil and the
+ * device fields are created on first use and cached by the descriptor's content; each call is one pipelined
+ * upload | sweep | download (neptune_rt_apply_host). Uses a lazily created default ctx (the analogue of
+ * neptune_rt_init_noargs, NeptunePETScRuntime.cpp:91-98) and aborts on failure like the reference's shims
+ * (NeptunePETScRuntime.cpp:15-30): generated code does not check statuses. */
+void neptune_rt_apply_memref_1d(const neptune_rt_stencil_desc *desc, int n_in, const neptune_rt_memref_1d *in, const neptune_rt_memref_1d *out);
+void neptune_rt_apply_memref_2d(const neptune_rt_stencil_desc *desc, int n_in, const neptune_rt_memref_2d *in, const neptune_rt_memref_2d *out);
+void neptune_rt_apply_memref_3d(const neptune_rt_stencil_desc *desc, int n_in, const neptune_rt_memref_3d *in, const neptune_rt_memref_3d *out);
+/* The same on bare host pointers to contiguous row-major boxes (offset 0, identity strides). */
 void neptune_rt_apply_memref(const neptune_rt_stencil_desc *desc, int n_in,
                              const void *const *in_host, void *out_host);
+/* Releases the stencils and device fields the memref entry points cached. */
+void neptune_rt_memref_cache_clear(void);
 
 #ifdef __cplusplus
 }

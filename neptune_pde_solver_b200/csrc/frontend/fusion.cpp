@@ -113,6 +113,7 @@ std::shared_ptr<Apply> fuse_pair(const Apply &p, const Apply &c, int k) {
 int fuse_applies(Module &m, bool fma, const std::function<bool(uint64_t)> &accept) {
   int fused = 0;
   for (auto &fn : m.functions) {
+    if (fn.rejected) continue;
     bool changed = true;
     while (changed) {
       changed = false;

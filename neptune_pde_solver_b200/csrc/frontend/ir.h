@@ -80,6 +80,9 @@ struct Function {
   std::vector<std::pair<std::string, Type>> args;
   std::vector<Type> results;
   std::vector<HostOp> ops;
+  // a function the pipeline could not lower (parser.cpp parse_function_body, module.cpp): kept with its diagnostic
+  bool rejected = false, unsupported = false;
+  std::string diagnostic;
 };
 
 struct Module {

@@ -378,7 +378,8 @@ int bind_args(neptune_b200_module &m, neptune_rt_ctx *ctx, const Function &fn, s
   if (v.empty()) {
     v.assign(fn.args.size(), nullptr);
     for (size_t i = 0; i < fn.args.size(); ++i) {
-      const Type &t = fi.arg_field[i];
+      // func.func: the field type a memref argument is wrapped as; operator definitions take temps directly
+      const Type &t = fn.kind == "func" ? fi.arg_field[i] : fn.args[i].second;
       if (t.kind != Type::Grid) continue;
       if (int rc = neptune_rt_field_alloc(ctx, t.dtype, t.bounds.rank(), t.bounds.lb.data(), t.bounds.ub.data(), &v[i])) {
         m.err = neptune_rt_last_error(ctx);
@@ -427,19 +428,84 @@ extern "C" int neptune_b200_compile(const char *text, const char *pipeline, nept
   m->fma = fma;
   try {
     m->mod = parse_module(text);
-    if (fuse) m->n_fused = fuse_applies(m->mod, fma, [](uint64_t key) { return neptune_rt_body_compiled(key) != 0; });
-    for (auto &fn : m->mod.functions)
-      for (auto &op : fn.ops)
-        if (op.kind == HostOp::ApplyOp) {
-          ApplyRec r;
-          r.function = fn.name;
-          r.ap = op.apply.get();
-          r.desc = recognize_apply(*op.apply, fma);
-          r.cuda_source = generate_functor(r.desc.c);
-          m->apply_index[op.apply.get()] = (int)m->applies.size();
-          m->applies.push_back(std::move(r));
+    auto reject = [](Function &fn, const Diagnostic &d) {
+      fn.ops.clear();
+      fn.rejected = true;
+      fn.unsupported = d.unsupported;
+      fn.diagnostic = d.what();
+    };
+    // a function that calls a rejected operator cannot be lowered either (to a fixed point: calls nest)
+    for (bool changed = true; changed;) {
+      changed = false;
+      for (auto &fn : m->mod.functions) {
+        if (fn.rejected) continue;
+        for (auto &op : fn.ops) {
+          if (op.kind != HostOp::ApplyLinear) continue;
+          const Function *callee = m->mod.find(op.callee);
+          if (callee && callee->rejected) {
+            reject(fn, Diagnostic("line " + std::to_string(op.line) + ": calls " + op.callee + ", which is not lowered: " + callee->diagnostic, callee->unsupported));
+            changed = true;
+            break;
+          }
         }
-    for (auto &fn : m->mod.functions) analyze_function(*m, fn, m->fns[fn.name]);
+      }
+    }
+    if (fuse) m->n_fused = fuse_applies(m->mod, fma, [](uint64_t key) { return neptune_rt_body_compiled(key) != 0; });
+    for (auto &fn : m->mod.functions) {
+      if (fn.rejected) continue;
+      // recognise every apply of the function first: one body outside the recognised set rejects the function
+      std::vector<ApplyRec> recs;
+      try {
+        for (auto &op : fn.ops)
+          if (op.kind == HostOp::ApplyOp) {
+            ApplyRec r;
+            r.function = fn.name;
+            r.ap = op.apply.get();
+            r.desc = recognize_apply(*op.apply, fma);
+            r.cuda_source = generate_functor(r.desc.c);
+            recs.push_back(std::move(r));
+          }
+      } catch (const Diagnostic &d) {
+        reject(fn, d);
+        continue;
+      }
+      for (auto &r : recs) {
+        m->apply_index[r.ap] = (int)m->applies.size();
+        m->applies.push_back(std::move(r));
+      }
+    }
+    for (bool changed = true; changed;) {   // rejections found by the recogniser propagate to callers as well
+      changed = false;
+      for (auto &fn : m->mod.functions) {
+        if (fn.rejected) continue;
+        for (auto &op : fn.ops) {
+          const Function *callee = op.kind == HostOp::ApplyLinear ? m->mod.find(op.callee) : nullptr;
+          if (callee && callee->rejected) {
+            reject(fn, Diagnostic("line " + std::to_string(op.line) + ": calls " + op.callee + ", which is not lowered: " + callee->diagnostic, callee->unsupported));
+            changed = true;
+            break;
+          }
+        }
+      }
+    }
+    // (applies of functions rejected in that second round stay in the table; nothing runs them)
+    int lowered = 0;
+    for (auto &fn : m->mod.functions) {
+      if (fn.rejected) continue;
+      try {
+        analyze_function(*m, fn, m->fns[fn.name]);
+        ++lowered;
+      } catch (const Diagnostic &d) {
+        m->fns.erase(fn.name);
+        reject(fn, d);
+      }
+    }
+    if (lowered == 0) {
+      // nothing of the module is on the B200 path: fail with the first diagnostic, as a failed conversion does
+      for (auto &fn : m->mod.functions)
+        if (fn.rejected) throw Diagnostic(fn.diagnostic, fn.unsupported);
+      throw Diagnostic("the module holds no function");
+    }
   } catch (const Diagnostic &d) {
     report(d.what());
     const int rc = d.unsupported ? NEPTUNE_RT_EUNSUPPORTED : NEPTUNE_RT_EINVAL;
@@ -480,7 +546,11 @@ extern "C" const char *neptune_b200_apply_cuda_source(neptune_b200_module *m, in
 extern "C" const char *neptune_b200_function_plan(neptune_b200_module *m, const char *fn) {
   if (!m || !fn) return nullptr;
   auto it = m->fns.find(fn);
-  return it == m->fns.end() ? nullptr : it->second.plan.c_str();
+  if (it == m->fns.end()) {
+    const Function *f = m->mod.find(fn);
+    return (f && f->rejected) ? f->diagnostic.c_str() : nullptr;   // the diagnostic stands where the plan would
+  }
+  return it->second.plan.c_str();
 }
 extern "C" int neptune_b200_function_arg_count(neptune_b200_module *m, const char *fn) {
   if (!m || !fn) return -1;
@@ -495,6 +565,15 @@ extern "C" int64_t neptune_b200_function_arg_numel(neptune_b200_module *m, const
   return t.kind == Type::Grid ? t.bounds.numel() : -1;
 }
 extern "C" const char *neptune_b200_last_error(neptune_b200_module *m) { return m ? m->err.c_str() : ""; }
+extern "C" int neptune_b200_function_count(neptune_b200_module *m) { return m ? (int)m->mod.functions.size() : 0; }
+extern "C" const char *neptune_b200_function_name(neptune_b200_module *m, int i) {
+  return (m && i >= 0 && i < (int)m->mod.functions.size()) ? m->mod.functions[(size_t)i].name.c_str() : nullptr;
+}
+extern "C" const char *neptune_b200_function_diagnostic(neptune_b200_module *m, const char *fn) {
+  if (!m || !fn) return nullptr;
+  const Function *f = m->mod.find(fn);
+  return (f && f->rejected) ? f->diagnostic.c_str() : nullptr;
+}
 
 extern "C" neptune_rt_stencil *neptune_b200_apply_stencil(neptune_b200_module *m, neptune_rt_ctx *ctx, int index) {
   if (!m || !ctx || index < 0 || index >= (int)m->applies.size()) return nullptr;
@@ -507,7 +586,28 @@ extern "C" int neptune_b200_run_host(neptune_b200_module *m, neptune_rt_ctx *ctx
   if (!m || !ctx || !function || (n_args > 0 && !args)) return NEPTUNE_RT_EINVAL;
   const Function *fn = m->mod.find(function);
   if (!fn) { m->err = std::string("no function ") + function; return NEPTUNE_RT_EINVAL; }
-  if (fn->kind != "func") { m->err = "only func.func entries can be run from host buffers"; return NEPTUNE_RT_EINVAL; }
+  if (fn->rejected) {
+    m->err = std::string(function) + " was not lowered by neptuneir-to-b200: " + fn->diagnostic;
+    return fn->unsupported ? NEPTUNE_RT_EUNSUPPORTED : NEPTUNE_RT_EINVAL;
+  }
+  if (fn->kind != "func") {
+    // an operator definition (linear_opdef / nonlinear_opdef), called the way StructureLowering.cpp:31-140 makes it
+    // callable (func.func + func.call): args[0 .. n) are host buffers of its temp operands, args[n] receives the result
+    if ((int)fn->args.size() + 1 != n_args) { m->err = "an operator definition takes its operands plus one result buffer"; return NEPTUNE_RT_EINVAL; }
+    std::vector<neptune_rt_field *> *fields = nullptr;
+    if (int rc = bind_args(*m, ctx, *fn, &fields)) return rc;
+    for (size_t i = 0; i < fn->args.size(); ++i)
+      if ((*fields)[i])
+        if (int rc = neptune_rt_field_upload((*fields)[i], args[i])) { m->err = neptune_rt_last_error(ctx); return rc; }
+    Exec ex{*m, ctx, m->per_ctx[ctx], {}};
+    ex.pc.cursor.clear();
+    neptune_rt_field *ret = nullptr;
+    if (int rc = ex.run(*fn, *fields, &ret)) return rc;
+    if (!ret) { m->err = "the operator returned no temp"; return NEPTUNE_RT_EINVAL; }
+    if (int rc = neptune_rt_field_download(ret, args[n_args - 1])) { m->err = neptune_rt_last_error(ctx); return rc; }
+    if (int rc = neptune_rt_sync(ctx)) { m->err = neptune_rt_last_error(ctx); return rc; }
+    return NEPTUNE_RT_OK;
+  }
   if ((int)fn->args.size() != n_args) { m->err = "argument count mismatch"; return NEPTUNE_RT_EINVAL; }
   const FnInfo &fi = m->fns.at(fn->name);
   std::vector<neptune_rt_field *> *fields = nullptr;
@@ -550,6 +650,10 @@ extern "C" int neptune_b200_run_steps_host(neptune_b200_module *m, neptune_rt_ct
   if (!m || !ctx || !function || n_args < 2 || !args || nsteps < 0) return NEPTUNE_RT_EINVAL;
   const Function *fn = m->mod.find(function);
   if (!fn) { m->err = std::string("no function ") + function; return NEPTUNE_RT_EINVAL; }
+  if (fn->rejected) {
+    m->err = std::string(function) + " was not lowered by neptuneir-to-b200: " + fn->diagnostic;
+    return fn->unsupported ? NEPTUNE_RT_EUNSUPPORTED : NEPTUNE_RT_EINVAL;
+  }
   if (fn->kind != "func" || (int)fn->args.size() != n_args) { m->err = "argument count mismatch"; return NEPTUNE_RT_EINVAL; }
   const FnInfo &fi = m->fns.at(fn->name);
   std::vector<neptune_rt_field *> *fields = nullptr;
@@ -564,16 +668,40 @@ extern "C" int neptune_b200_run_steps_host(neptune_b200_module *m, neptune_rt_ct
     if ((*fields)[i] && (fi.arg_needs_upload[i] || (i == 1 && fi.arg_needs_upload[0])))
       if (int rc = neptune_rt_field_upload((*fields)[i], args[i])) { m->err = neptune_rt_last_error(ctx); return rc; }
   Exec ex{*m, ctx, m->per_ctx[ctx], {}};
+  // step t writes host argument (t even ? 0 : 1)
+  const int res = nsteps == 0 ? 1 : ((nsteps - 1) % 2 == 0 ? 0 : 1);
+  neptune_rt_field *last = (*fields)[res];
+  if (fi.pipe_apply >= 0 && fi.pipe_out_arg == 0 && !fi.pipe_in_args.empty() && fi.pipe_in_args[0] == 1) {
+    // entry(out, in, extra...) = ONE apply of `in` (+ pointwise/coefficient arguments) stored whole into `out`: the
+    // swapped host loop is exactly neptune_rt_run_steps, which fuses pairs of steps into temporally blocked
+    // launches where the body has such a kernel (bitwise the same as nsteps single sweeps)
+    int rc = 0;
+    neptune_rt_stencil *st = ex.stencil(m->apply_index.at(fn->ops[fi.pipe_apply].apply.get()), &rc);
+    if (!st) return rc;
+    std::vector<neptune_rt_field *> extra;
+    for (size_t k = 1; k < fi.pipe_in_args.size(); ++k) extra.push_back((*fields)[fi.pipe_in_args[k]]);
+    bool distinct = true;   // a time loop replaces input 0 only: the other inputs must be other arguments
+    for (size_t k = 1; k < fi.pipe_in_args.size(); ++k) distinct &= fi.pipe_in_args[k] >= 2;
+    if (distinct) {
+      if ((rc = neptune_rt_run_steps(st, (*fields)[1], (*fields)[0], (int)extra.size(), extra.data(), nsteps, &last))) {
+        m->err = neptune_rt_last_error(ctx);
+        return rc;
+      }
+      if (nsteps > 0)
+        if ((rc = neptune_rt_field_download(last, args[res]))) { m->err = neptune_rt_last_error(ctx); return rc; }
+      if (result_arg) *result_arg = res;
+      if ((rc = neptune_rt_sync(ctx))) { m->err = neptune_rt_last_error(ctx); return rc; }
+      return NEPTUNE_RT_OK;
+    }
+  }
   std::vector<neptune_rt_field *> cur = *fields;
   for (int64_t t = 0; t < nsteps; ++t) {
     ex.pc.cursor.clear();
     if (int rc = ex.run(*fn, cur, nullptr)) return rc;
     std::swap(cur[0], cur[1]);
   }
-  // step t writes host argument (t even ? 0 : 1)
-  const int res = nsteps == 0 ? 1 : ((nsteps - 1) % 2 == 0 ? 0 : 1);
   if (nsteps > 0)
-    if (int rc = neptune_rt_field_download((*fields)[res], args[res])) { m->err = neptune_rt_last_error(ctx); return rc; }
+    if (int rc = neptune_rt_field_download(last, args[res])) { m->err = neptune_rt_last_error(ctx); return rc; }
   if (result_arg) *result_arg = res;
   if (int rc = neptune_rt_sync(ctx)) { m->err = neptune_rt_last_error(ctx); return rc; }
   return NEPTUNE_RT_OK;

@@ -155,6 +155,11 @@ class Lexer {
   int line_ = 1;
   bool have_ = false;
   Tok cur_;
+
+ public:
+  struct State { size_t pos; int line; bool have; Tok cur; };
+  State save() const { return State{pos_, line_, have_, cur_}; }
+  void restore(const State &st) { pos_ = st.pos; line_ = st.line; have_ = st.have; cur_ = st.cur; }
 };
 
 struct AttrValue {
@@ -390,7 +395,7 @@ class Parser {
       }
       if (accept_word("attributes")) skip_braces();
       expect("{");
-      while (!accept("}")) fn.ops.push_back(parse_host_op());
+      parse_function_body(fn);
       return fn;
     }
     if (t.kind == Tok::Word && (t.text == "neptune_ir.linear_opdef" || t.text == "neptune_ir.nonlinear_opdef")) {
@@ -414,10 +419,34 @@ class Parser {
       if (fn.args.size() != in_tys.size()) fail("opdef block argument count differs from its signature");
       for (size_t i = 0; i < in_tys.size(); ++i)
         if (fn.args[i].second != in_tys[i]) fail("opdef block argument types differ from its signature");
-      while (!accept("}")) fn.ops.push_back(parse_host_op());
+      parse_function_body(fn);
       return fn;
     }
     throw Diagnostic("line " + std::to_string(t.line) + ": unsupported top-level operation '" + t.text + "'", true);
+  }
+
+  // The operations of a function up to its closing brace.  A function that holds something outside the hot path
+  // (neptune_ir.time_advance, solve_linear, a body with control flow ...) or that breaks a verifier rule is kept
+  // as a REJECTED function carrying the diagnostic, and parsing resumes after its closing brace: the other
+  // functions of the module — the operator definitions a time_advance refers to, for one — are still lowered.
+  // (The reference's conversion fails the whole module; a module none of whose functions lowers still fails here.)
+  void parse_function_body(Function &fn) {
+    const Lexer::State at_open = lx_.save();
+    try {
+      while (!accept("}")) fn.ops.push_back(parse_host_op());
+    } catch (const Diagnostic &d) {
+      fn.ops.clear();
+      fn.rejected = true;
+      fn.unsupported = d.unsupported;
+      fn.diagnostic = d.what();
+      lx_.restore(at_open);
+      for (int depth = 1; depth > 0;) {
+        Tok t = lx_.next();
+        if (t.kind == Tok::Eof) throw Diagnostic(fn.diagnostic + " (and the function's closing brace is missing)", d.unsupported);
+        if (t.kind == Tok::Punct && t.text == "{") ++depth;
+        if (t.kind == Tok::Punct && t.text == "}") --depth;
+      }
+    }
   }
 
   HostOp parse_host_op() {
@@ -538,6 +567,8 @@ class Parser {
       unsigned long long bits = std::stoull(s, nullptr, 16);
       if (dtype == NEPTUNE_RT_F32) { uint32_t b = (uint32_t)bits; float f; std::memcpy(&f, &b, 4); v = f; }
       else std::memcpy(&v, &bits, 8);
+    } else if (dtype == NEPTUNE_RT_F32) {
+      v = (double)std::strtof(s.c_str(), nullptr);   // one rounding, decimal -> f32, as APFloat does (not decimal -> f64 -> f32)
     } else {
       v = std::strtod(s.c_str(), nullptr);
     }

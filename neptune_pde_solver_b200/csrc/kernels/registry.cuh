@@ -10,6 +10,7 @@
 #include "sweep_tb2m.cuh"
 #include "sweep_tb2g.cuh"
 #include "sweep_tb2p.cuh"
+#include "sweep_tb2q.cuh"
 #include "sweep_rows.cuh"
 #include "sweep_rows2.cuh"
 
@@ -113,11 +114,12 @@ template <class F, class C, bool FMA> int launch_tma(const SweepArgs &a) {
 }
 
 // MARCH: 0 = sweep_tb2 (both levels through shared memory), 1 = sweep_tb2m (z-marching), 2 = sweep_tb2g (z-marching,
-// grouped), 3 = sweep_tb2p (grouped, phase B software-pipelined into phase A)
+// grouped), 3 = sweep_tb2p (grouped, phase B software-pipelined into phase A), 4 = sweep_tb2q (tb2p with a lean steady state)
 template <class F, class C, int MARCH> struct Tb2GeomOf { typedef Tb2Geom<F, C> type; };
 template <class F, class C> struct Tb2GeomOf<F, C, 1> { typedef Tb2mGeom<F, C> type; };
 template <class F, class C> struct Tb2GeomOf<F, C, 2> { typedef Tb2gGeom<F, C> type; };
 template <class F, class C> struct Tb2GeomOf<F, C, 3> { typedef Tb2pGeom<F, C> type; };
+template <class F, class C> struct Tb2GeomOf<F, C, 4> { typedef Tb2pGeom<F, C> type; };
 
 template <class F, class C, bool FMA, int MARCH = 0> int launch_tb2(const SweepArgs &a) {
   typedef typename Tb2GeomOf<F, C, MARCH>::type G;
@@ -125,6 +127,7 @@ template <class F, class C, bool FMA, int MARCH = 0> int launch_tb2(const SweepA
     if constexpr (MARCH == 1) return sweep_tb2m<F, C, FMA>;
     else if constexpr (MARCH == 2) return sweep_tb2g<F, C, FMA>;
     else if constexpr (MARCH == 3) return sweep_tb2p<F, C, FMA>;
+    else if constexpr (MARCH == 4) return sweep_tb2q<F, C, FMA>;
     else return sweep_tb2<F, C, FMA>;
   }();
   static int occ_cached[16] = {0};
@@ -280,7 +283,7 @@ template <class F, class C, bool FMA, int MARCH = 0> Variant tb2_variant(const c
   v.box_x = G::P0; v.box_y = G::BOX_Y;
   v.halo_x = 2 * G::VX; v.halo_y = 2;
   v.threads = G::THREADS; v.smem = G::SMEM_BYTES;
-  v.gap_dim = MARCH <= 1 ? 0 : -1;   // sweep_tb2, sweep_tb2m
+  v.gap_dim = (MARCH <= 1 || MARCH == 4) ? 0 : -1;   // sweep_tb2, sweep_tb2m, sweep_tb2q
   v.launch = &launch_tb2<F, C, FMA, MARCH>;
   return v;
 }
@@ -379,6 +382,8 @@ template <class F> struct BodyRegistrar {
             e.variants.push_back(tb2_variant<F, Tb2pA, false, 3>("tb2p:128x14"));
             e.variants.push_back(tb2_variant<F, Tb2pB, false, 3>("tb2p:64x24"));
             e.variants.push_back(tb2_variant<F, Tb2pA, true, 3>("tb2p:128x14"));
+            e.variants.push_back(tb2_variant<F, Tb2pA, false, 4>("tb2q:128x14"));
+            e.variants.push_back(tb2_variant<F, Tb2pA, true, 4>("tb2q:128x14"));
           }
         } else if constexpr (F::NIN == 2 && F::RZ == 1 && F::ZSTAR) {
           // input 0 plus pointwise inputs (Jacobi with a right-hand side): the z-marching form only

@@ -1,0 +1,348 @@
+// Temporally blocked z-march, lean steady state (sm_100a): sweep_tb2p's data movement with a steady-state
+// group that carries no per-point bookkeeping.
+//
+// r01 ncu of sweep_tb2p on C3 (profiles/r01_c3_tb2p_128x14_ncu.txt): 42.5 thread instructions per point-update
+// against 9 fp64 operations; the steady loop is 832 SASS instructions per three planes of which 216 are DADD/DMUL,
+// 96 FSEL (copy-through selects), 32 SEL, 45 ISETP, 22 BRA, ~250 IMAD/VIADD/LOP3/LEA/R2UR/LDC (masks, slot
+// addresses, window rotation moves).  Here
+//   * the z windows of both levels live in THREE statically indexed register blocks, slot (step + q) mod 3, so a
+//     group of three planes ends where it began and no register is moved;
+//   * a group whose three steps are all in steady state AND whose planes all lie inside the apply's z bounds takes
+//     the lean path: both levels are evaluated unconditionally in one basic block (eight independent fp64 chains
+//     per thread), then ONE branch that only threads with a point outside the y/x bounds take applies the
+//     copy-through selects, then the stores go out under per-item row predicates;
+//   * every other group (pipeline fill and drain, the first and last planes of the box) runs the fully masked
+//     step of sweep_tb2p.
+// Ring threads evaluate level 2 as well (its loads stay inside the guarded rings) and simply store nothing: a
+// warp instruction costs the same with or without them, and the branch that used to skip them split the stream.
+// Arithmetic is the body functor at both levels: bit-identical to two single sweeps.
+#pragma once
+#include "sweep_tb2p.cuh"
+
+namespace neptune {
+
+
+// Shared-memory access by 32-bit shared-window address + immediate byte offset.  Generic pointers into dynamic
+// shared memory made ptxas rebuild the window base (S2R SR_CgaCtaId + LEA) inside the plane loop when registers ran out.
+template <int OFF> __device__ __forceinline__ void lds16(double (&d)[2], uint32_t addr) {
+  asm volatile("ld.shared.v2.f64 {%0, %1}, [%2+%3];" : "=d"(d[0]), "=d"(d[1]) : "r"(addr), "n"(OFF));
+}
+template <int OFF> __device__ __forceinline__ void lds16(float (&d)[4], uint32_t addr) {
+  asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4+%5];" : "=f"(d[0]), "=f"(d[1]), "=f"(d[2]), "=f"(d[3]) : "r"(addr), "n"(OFF));
+}
+template <int OFF> __device__ __forceinline__ double lds1(uint32_t addr, double) {
+  double v;
+  asm volatile("ld.shared.f64 %0, [%1+%2];" : "=d"(v) : "r"(addr), "n"(OFF));
+  return v;
+}
+template <int OFF> __device__ __forceinline__ float lds1(uint32_t addr, float) {
+  float v;
+  asm volatile("ld.shared.f32 %0, [%1+%2];" : "=f"(v) : "r"(addr), "n"(OFF));
+  return v;
+}
+template <int OFF> __device__ __forceinline__ void sts16(uint32_t addr, const double (&d)[2]) {
+  asm volatile("st.shared.v2.f64 [%0+%1], {%2, %3};" ::"r"(addr), "n"(OFF), "d"(d[0]), "d"(d[1]) : "memory");
+}
+template <int OFF> __device__ __forceinline__ void sts16(uint32_t addr, const float (&d)[4]) {
+  asm volatile("st.shared.v4.f32 [%0+%1], {%2, %3, %4, %5};" ::"r"(addr), "n"(OFF), "f"(d[0]), "f"(d[1]), "f"(d[2]), "f"(d[3]) : "memory");
+}
+// one elected lane arrives, without a branch
+__device__ __forceinline__ void mbar_arrive_if(uint32_t bar, bool pred) {
+  asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.u32 p, %1, 0;\n\t@p mbarrier.arrive.shared::cta.b64 _, [%0];\n\t}" ::"r"(bar), "r"((uint32_t)pred) : "memory");
+}
+
+// in-plane halo of a VY x VX block at shared address `blk` (row pitch PB bytes) into the window c[][] (centre left to
+// the caller); `lr` = blk + (swap ? 16 : -S), `rl` = blk + (swap ? -S : 16): lane groups of eight alternate the order of
+// the left/right reads so that the 8-byte reads at a 16-byte lane stride do not bank-conflict (sweep_tb2m.cuh)
+template <class T, int VX, int VY, int PB, bool CORNERS>
+__device__ __forceinline__ void load_halo_s(T (&c)[VY + 2][VX + 2], uint32_t blk, uint32_t lr, uint32_t rl, bool swap) {
+  T t[VX], b[VX];
+  lds16<-PB>(t, blk);
+  lds16<VY * PB>(b, blk);
+#pragma unroll
+  for (int i = 0; i < VX; ++i) { c[0][1 + i] = t[i]; c[VY + 1][1 + i] = b[i]; }
+  if constexpr (CORNERS) {   // bodies with in-plane diagonal taps only
+    constexpr int S = (int)sizeof(T);
+    c[0][0] = lds1<-PB - S>(blk, T());
+    c[0][VX + 1] = lds1<-PB + VX * S>(blk, T());
+    c[VY + 1][0] = lds1<VY * PB - S>(blk, T());
+    c[VY + 1][VX + 1] = lds1<VY * PB + VX * S>(blk, T());
+  }
+  static_for<VY>([&](auto rc) {
+    constexpr int R = decltype(rc)::value;
+    const T v1 = lds1<R * PB>(lr, T()), v2 = lds1<R * PB>(rl, T());
+    c[1 + R][0] = swap ? v2 : v1;
+    c[1 + R][VX + 1] = swap ? v1 : v2;
+  });
+}
+
+template <class F, class C, bool FMA>
+__global__ void __launch_bounds__((Tb2pGeom<F, C>::THREADS), C::MINB)
+sweep_tb2q(const __grid_constant__ KParams<F> p, const __grid_constant__ CUtensorMap tmap) {
+  typedef Tb2pGeom<F, C> G;
+  typedef typename F::T T;
+  constexpr int VX = G::VX, VY = G::VY, NS = G::NS;
+  constexpr int NCW = G::CONSUMERS / 32;
+  constexpr int GS = G::GS, NL1 = G::NL1;
+  static_assert(GS == 3, "the three-slot z windows need three planes per group");
+  constexpr int LAG = GS + 2;
+  constexpr unsigned ALL = (1u << (VY * VX)) - 1u;
+
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  unsigned char *smem = smem_raw + ((128u - (smem_u32(smem_raw) & 127u)) & 127u);
+  unsigned char *l0 = smem + G::GUARD_BYTES;
+  unsigned char *l1 = l0 + NS * G::SLOT_BYTES + G::GUARD_BYTES + G::L1_GUARD;
+  const uint32_t full0 = smem_u32(l1 + G::NL1 * G::L1_BYTES + G::L1_GUARD);
+  const uint32_t empty0 = full0 + 8 * NS;
+  const uint32_t stage0 = smem_u32(l0);
+
+  const int tid = threadIdx.x;
+  if (tid == 0) {
+    for (int s = 0; s < NS; ++s) {
+      mbar_init(full0 + 8 * s, 1);
+      mbar_init(empty0 + 8 * s, NCW);
+    }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
+
+  auto geom = [&](int item, int &zb, int &ze, int &y0, int &x0) {
+    const int ncols = p.ncx * p.ncy;
+    const int chunk = item / ncols, col = item - chunk * ncols;
+    const int cx = col / p.ncy, cy = col - cx * p.ncy;
+    zb = p.wlo[0] + chunk * p.zchunk + (chunk ? p.zgap : 0);
+    ze = min(p.whi[0], zb + p.zchunk);
+    y0 = (p.cyo + cy) * C::TY;
+    x0 = (p.cxo + cx) * C::TX;
+  };
+
+  if (tid >= G::CONSUMERS) {
+    if (tid == G::CONSUMERS) {
+      unsigned n = 0;
+      for (int item = blockIdx.x; item < p.nitems; item += gridDim.x) {
+        int zb, ze, y0, x0;
+        geom(item, zb, ze, y0, x0);
+        const int nslots = ze - zb + 4;
+        for (int j = 0; j < nslots; ++j, ++n) {
+          const unsigned s = n % NS;
+          mbar_wait(empty0 + 8 * s, ((n / NS) & 1) ^ 1);
+          mbar_expect_tx(full0 + 8 * s, G::STAGE_TX_BYTES);
+          tma_load_3d(stage0 + s * G::SLOT_BYTES, &tmap, x0 - 2 * VX, y0 - 2, zb - 2 + j, full0 + 8 * s);
+        }
+      }
+    }
+    return;
+  }
+
+  // ---- consumers ----------------------------------------------------------------------------------
+  constexpr int S = (int)sizeof(T);
+  constexpr int PB0 = G::P0 * S, PB1 = G::P1 * S;   // row pitches in bytes
+  constexpr bool CORNERS = F::XYDIAG;
+  const bool active = tid < G::ACTIVE;
+  const int bx = active ? tid % G::NBX : 0, by = active ? tid / G::NBX : 0;
+  const bool inner = active && bx >= 1 && bx <= G::NBX - 2 && by >= 1 && by <= G::NBY - 2;
+  const bool lane0 = (tid & 31) == 0;
+  const bool swap = ((tid >> 3) & 1) != 0;
+  // this thread's block inside level-0 slot 0 / level-1 plane 0, as shared-window byte addresses
+  const uint32_t t0 = stage0 + (uint32_t)(((by * VY - VY + 2) * G::P0 + VX + bx * VX) * S);
+  const uint32_t t1 = smem_u32(l1) + (uint32_t)(((by * VY) * G::P1 + bx * VX) * S);
+  int o_lr = swap ? VX * S : -S, o_rl = swap ? -S : VX * S;   // first / second of the left-right halo reads
+  uint32_t swp = swap ? 1u : 0u, ln0 = lane0 ? 1u : 0u, fullb = full0, emptyb = empty0;
+  // opaque to the compiler from here on: under register pressure ptxas otherwise rebuilds these from SR_TID /
+  // SR_CgaCtaId inside the plane loop (S2R + LOP3 + SEL + LEA per step)
+  asm volatile("" : "+r"(o_lr), "+r"(o_rl), "+r"(swp), "+r"(ln0), "+r"(fullb), "+r"(emptyb));
+  unsigned s = 0, ph = 0;   // level-0 ring slot / phase of the next plane to arrive
+  unsigned c1 = 0;          // level-1 ring slot phase A writes at the current step
+  // z windows, slot (R + q) mod 3 at step R of a group: a[.] = level-0 centre blocks of planes k-2, k-1, k;
+  // b[.] = level-1 centre blocks of planes k-LAG-1, k-LAG, k-LAG+1
+  T a[3][VY][VX], b[3][VY][VX];
+#pragma unroll
+  for (int q = 0; q < 3; ++q)
+#pragma unroll
+    for (int iy = 0; iy < VY; ++iy)
+#pragma unroll
+      for (int ix = 0; ix < VX; ++ix) a[q][iy][ix] = b[q][iy][ix] = T(0);
+  T nopw[1][VY][VX];
+#pragma unroll
+  for (int iy = 0; iy < VY; ++iy)
+#pragma unroll
+    for (int ix = 0; ix < VX; ++ix) nopw[0][iy][ix] = T(0);
+
+  auto slot = [](unsigned base, unsigned d) { const unsigned v = base + d; return v >= (unsigned)NL1 ? v - (unsigned)NL1 : v; };
+
+  for (int item = blockIdx.x; item < p.nitems; item += gridDim.x) {
+    int zb, ze, y0, x0;
+    geom(item, zb, ze, y0, x0);
+    const int gx = x0 - VX + bx * VX, gy = y0 - VY + by * VY;
+    unsigned bmask = 0, wmask = 0;
+#pragma unroll
+    for (int iy = 0; iy < VY; ++iy)
+#pragma unroll
+      for (int ix = 0; ix < VX; ++ix) {
+        const int y = gy + iy, x = gx + ix;
+        if (y >= p.blo[1] && y < p.bhi[1] && x >= p.blo[2] && x < p.bhi[2]) bmask |= 1u << (iy * VX + ix);
+        if (inner && y >= p.wlo[1] && y < p.whi[1] && x >= p.wlo[2] && x < p.whi[2]) wmask |= 1u << (iy * VX + ix);
+      }
+    unsigned nb = ~bmask & ALL;          // points of this thread that copy through in (y, x)
+    asm volatile("" : "+r"(nb), "+r"(wmask), "+r"(bmask));   // as integers, not as eight predicates recombined every step
+    const int nslots = ze - zb + 4;
+    // steps j whose phase-A plane (zb - 3 + j) and phase-B' plane (zb - 7 + j) both lie inside the z bounds
+    // (and not the item's last arrival, whose stage is handed back at once)
+    const int jz_lo = max(p.blo[0] - zb + 7, LAG + 2), jz_hi = min(p.bhi[0] - zb + 3, nslots - 1);
+    const int g_lo = (jz_lo + GS - 1) / GS * GS;               // first lean group
+    const int n_lean = jz_hi - g_lo >= GS ? (jz_hi - g_lo) / GS : 0;
+    T *dst = p.out + (long long)zb * p.out_sz + (long long)gy * p.out_sy + gx;
+    uint32_t prv = t0;        // this thread's block inside the stage of plane k-1
+    unsigned s_prv = 0;
+
+    for (int j0 = 0; j0 < nslots + GS; j0 += GS) {
+      if (j0 == g_lo && n_lean > 0) {
+        // ---- lean groups: three steady steps, every plane inside the z bounds ------------------------
+        for (int g = n_lean; g > 0; --g)
+        static_for<GS>([&](auto rc) {
+          constexpr int R = decltype(rc)::value;
+          constexpr int A0 = R % 3, A1 = (R + 1) % 3, A2 = (R + 2) % 3;
+          T wa[VY + 2][VX + 2], wb[VY + 2][VX + 2];
+          mbar_wait(fullb + 8 * s, ph);
+          const uint32_t cur = t0 + s * (uint32_t)G::SLOT_BYTES;
+          static_for<VY>([&](auto r) { lds16<decltype(r)::value * PB0>(a[A2][decltype(r)::value], cur); });
+          load_halo_s<T, VX, VY, PB0, CORNERS>(wa, prv, prv + o_lr, prv + o_rl, swp != 0u);
+          __syncwarp();
+          mbar_arrive_if(emptyb + 8 * s_prv, ln0 != 0u);
+          s_prv = s;
+          prv = cur;
+          if (++s == NS) { s = 0; ph ^= 1; }
+          // level-1 reads of phase B' (planes produced before the last barrier)
+          const uint32_t pnew = t1 + slot(c1, GS + 1) * (uint32_t)G::L1_BYTES;   // plane k-LAG+1
+          const uint32_t pctr = t1 + slot(c1, GS) * (uint32_t)G::L1_BYTES;       // plane k-LAG
+          static_for<VY>([&](auto r) { lds16<decltype(r)::value * PB1>(b[A2][decltype(r)::value], pnew); });
+          load_halo_s<T, VX, VY, PB1, CORNERS>(wb, pctr, pctr + o_lr, pctr + o_rl, swp != 0u);
+#pragma unroll
+          for (int iy = 0; iy < VY; ++iy)
+#pragma unroll
+            for (int ix = 0; ix < VX; ++ix) { wa[1 + iy][1 + ix] = a[A1][iy][ix]; wb[1 + iy][1 + ix] = b[A1][iy][ix]; }
+          // both levels, unconditionally, one basic block
+          T ra[VY][VX], res[VY][VX];
+          static_for<VY>([&](auto iyc) {
+            constexpr int IY = decltype(iyc)::value;
+            static_for<VX>([&](auto ixc) {
+              constexpr int IX = decltype(ixc)::value;
+              MarchAcc<F, VY, VX, IY, IX> acca{a[A0], wa, a[A2], nopw};
+              ra[IY][IX] = F::template eval<FMA>(acca, p.c);
+              MarchAcc<F, VY, VX, IY, IX> accb{b[A0], wb, b[A2], nopw};
+              res[IY][IX] = F::template eval<FMA>(accb, p.c);
+            });
+          });
+          if (nb != 0u) {   // threads on the y/x edge of the apply bounds only: copy-through of both levels
+            asm volatile("" ::: "memory");   // keeps this a branch: if-converted it is 32 selects per step for every thread
+#pragma unroll
+            for (int iy = 0; iy < VY; ++iy)
+#pragma unroll
+              for (int ix = 0; ix < VX; ++ix)
+                if ((nb >> (iy * VX + ix)) & 1u) { ra[iy][ix] = a[A1][iy][ix]; res[iy][ix] = b[A1][iy][ix]; }
+          }
+          const uint32_t l1p = t1 + c1 * (uint32_t)G::L1_BYTES;
+          static_for<VY>([&](auto r) { sts16<decltype(r)::value * PB1>(l1p, ra[decltype(r)::value]); });
+          if (wmask == ALL) {
+#pragma unroll
+            for (int iy = 0; iy < VY; ++iy) stg_vec<T, VX, false>(dst + iy * p.out_sy, res[iy]);
+          } else if (wmask != 0u) {   // tiles cut by the edge of the written box
+#pragma unroll
+            for (int iy = 0; iy < VY; ++iy)
+#pragma unroll
+              for (int ix = 0; ix < VX; ++ix)
+                if ((wmask >> (iy * VX + ix)) & 1u) dst[iy * p.out_sy + ix] = res[iy][ix];
+          }
+          dst += p.out_sz;
+          c1 = slot(c1, 1u);
+          if constexpr (R == GS - 1) asm volatile("bar.sync 1, %0;" ::"n"(G::CONSUMERS) : "memory");
+        });
+        j0 += GS * n_lean;
+      }
+      // ---- general group: pipeline fill / drain and planes on the z edge of the bounds (fully masked) ----
+      static_for<GS>([&](auto rc) {
+        constexpr int R = decltype(rc)::value;
+        constexpr int A0 = R % 3, A1 = (R + 1) % 3, A2 = (R + 2) % 3;
+        const int j = j0 + R;
+        const int k = zb - 2 + j;
+        const bool arrive = j < nslots;                          // a level-0 plane arrives at this step
+        const bool do_a = arrive && j >= 2;                      // ... and completes level-1 plane k-1
+        const bool push_b = j >= LAG && j < nslots + GS;         // level-1 plane k-LAG+1 exists
+        const bool do_b = j >= LAG + 2 && j < nslots + GS;       // level-2 plane k-LAG is wanted
+        T wa[VY + 2][VX + 2], wb[VY + 2][VX + 2];
+        if (arrive) {
+          mbar_wait(fullb + 8 * s, ph);
+          const uint32_t cur = t0 + s * (uint32_t)G::SLOT_BYTES;
+          static_for<VY>([&](auto r) { lds16<decltype(r)::value * PB0>(a[A2][decltype(r)::value], cur); });
+          if (do_a) load_halo_s<T, VX, VY, PB0, CORNERS>(wa, prv, prv + o_lr, prv + o_rl, swp != 0u);
+          __syncwarp();
+          mbar_arrive_if(emptyb + 8 * s_prv, ln0 != 0u && j >= 1);
+          mbar_arrive_if(emptyb + 8 * s, ln0 != 0u && j == nslots - 1);
+          s_prv = s;
+          prv = cur;
+          if (++s == NS) { s = 0; ph ^= 1; }
+        }
+        if (do_a) {
+#pragma unroll
+          for (int iy = 0; iy < VY; ++iy)
+#pragma unroll
+            for (int ix = 0; ix < VX; ++ix) wa[1 + iy][1 + ix] = a[A1][iy][ix];
+          const unsigned m = (k - 1 >= p.blo[0] && k - 1 < p.bhi[0]) ? bmask : 0u;
+          const uint32_t l1p = t1 + c1 * (uint32_t)G::L1_BYTES;
+          static_for<VY>([&](auto iyc) {
+            constexpr int IY = decltype(iyc)::value;
+            T ra[VX];
+            static_for<VX>([&](auto ixc) {
+              constexpr int IX = decltype(ixc)::value;
+              MarchAcc<F, VY, VX, IY, IX> acc{a[A0], wa, a[A2], nopw};
+              const T v = F::template eval<FMA>(acc, p.c);
+              ra[IX] = ((m >> (IY * VX + IX)) & 1u) ? v : a[A1][IY][IX];
+            });
+            sts16<IY * PB1>(l1p, ra);
+          });
+        }
+        if (push_b && wmask != 0) {
+          const uint32_t pnew = t1 + slot(c1, GS + 1) * (uint32_t)G::L1_BYTES;
+          static_for<VY>([&](auto r) { lds16<decltype(r)::value * PB1>(b[A2][decltype(r)::value], pnew); });
+          if (do_b) {
+            const uint32_t pctr = t1 + slot(c1, GS) * (uint32_t)G::L1_BYTES;
+            load_halo_s<T, VX, VY, PB1, CORNERS>(wb, pctr, pctr + o_lr, pctr + o_rl, swp != 0u);
+          }
+        }
+        if (do_b) {
+          if (wmask != 0) {
+#pragma unroll
+            for (int iy = 0; iy < VY; ++iy)
+#pragma unroll
+              for (int ix = 0; ix < VX; ++ix) wb[1 + iy][1 + ix] = b[A1][iy][ix];
+            const unsigned m = (k - LAG >= p.blo[0] && k - LAG < p.bhi[0]) ? bmask : 0u;
+            static_for<VY>([&](auto iyc) {
+              constexpr int IY = decltype(iyc)::value;
+              T res[VX];
+              static_for<VX>([&](auto ixc) {
+                constexpr int IX = decltype(ixc)::value;
+                MarchAcc<F, VY, VX, IY, IX> acc{b[A0], wb, b[A2], nopw};
+                const T v = F::template eval<FMA>(acc, p.c);
+                res[IX] = ((m >> (IY * VX + IX)) & 1u) ? v : b[A1][IY][IX];
+              });
+              constexpr unsigned ROW = ((1u << VX) - 1u) << (IY * VX);
+              T *d = dst + IY * p.out_sy;
+              if ((wmask & ROW) == ROW) {
+                stg_vec<T, VX, false>(d, res);
+              } else {
+#pragma unroll
+                for (int ix = 0; ix < VX; ++ix)
+                  if ((wmask >> (IY * VX + ix)) & 1u) d[ix] = res[ix];
+              }
+            });
+          }
+          dst += p.out_sz;
+        }
+        if (j >= 2 && j < nslots + GS) c1 = slot(c1, 1u);
+        if constexpr (R == GS - 1) asm volatile("bar.sync 1, %0;" ::"n"(G::CONSUMERS) : "memory");
+      });
+    }
+  }
+}
+
+}  // namespace neptune

@@ -11,12 +11,15 @@
 #include <cuda_runtime.h>
 #include <dlfcn.h>
 #include <nccl.h>
+#include <nvtx3/nvToolsExt.h>   // header-only: ranges show up when a profiler injects, cost nothing otherwise
 
 #include <algorithm>
 #include <cstdarg>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <functional>
+#include <initializer_list>
 #include <string>
 #include <vector>
 
@@ -46,6 +49,7 @@ struct NcclApi {
   ncclResult_t (*GroupStart)() = nullptr;
   ncclResult_t (*GroupEnd)() = nullptr;
   const char *(*GetErrorString)(ncclResult_t) = nullptr;
+  ncclResult_t (*CommGetAsyncError)(ncclComm_t, ncclResult_t *) = nullptr;   // optional
   bool ok = false;
 };
 
@@ -79,6 +83,7 @@ NcclApi &nccl() {
   NB_SYM(GroupStart, "ncclGroupStart");
   NB_SYM(GroupEnd, "ncclGroupEnd");
   NB_SYM(GetErrorString, "ncclGetErrorString");
+  NB_SYM(CommGetAsyncError, "ncclCommGetAsyncError");
 #undef NB_SYM
   api.ok = api.GetUniqueId && api.CommInitRank && api.CommDestroy && api.Send && api.Recv && api.AllReduce && api.GroupStart &&
            api.GroupEnd && api.GetErrorString;
@@ -86,6 +91,11 @@ NcclApi &nccl() {
 }
 
 thread_local std::string g_last_error;
+
+struct NvtxRange {   // ranges around the time loop and the host-memref sweep
+  explicit NvtxRange(const char *name) { nvtxRangePushA(name); }
+  ~NvtxRange() { nvtxRangePop(); }
+};
 }  // namespace
 
 // ---------------------------------------------------------------------------------------------
@@ -106,6 +116,14 @@ struct neptune_rt_ctx {
   std::string err;
   ncclComm_t comm = nullptr;
   int nranks = 1, rank = 0;
+  // slab mode: rank-local facts are agreed once per (stencil, fields) with a 4-int ncclAllReduce(min)
+  int *agree_dev = nullptr, *agree_host = nullptr;
+  // slab trace (neptune_rt_slab_trace): timing events of the last traced neptune_rt_run_steps
+  bool trace_on = false;
+  std::vector<cudaEvent_t> trace_events;   // 4 per launch group: begin, boundary done, exchange done, interior done
+  int trace_groups = 0;
+  std::vector<int> trace_kind;             // per group: steps advanced * 10 + (1 = exchanged)
+  std::vector<std::function<void()>> on_finalize;
 };
 
 struct neptune_rt_field {
@@ -143,6 +161,15 @@ struct neptune_rt_stencil {
   int64_t slab_ghost = 0, slab_glb0 = 0, slab_gub0 = 0;
   const Variant *last = nullptr;
   std::vector<TmapEntry> tmaps;
+  bool slab_loop = false;   // set by neptune_rt_run_steps around its slab launches: dim-0 bounds are the GLOBAL ones
+  // what the ranks agreed for the last (fields, settings) neptune_rt_run_steps saw in slab mode
+  struct Agreed {
+    bool valid = false, fuse2 = false, split = false;
+    neptune_rt_field *a = nullptr, *b = nullptr;
+    std::vector<neptune_rt_field *> extra;
+    int tblock = 0;
+    std::string want_tb;
+  } agreed;
 };
 
 namespace {
@@ -286,19 +313,29 @@ extern "C" int neptune_rt_init(int device, neptune_rt_ctx **out) {
   RT_CUDA(nullptr, cudaSetDevice(device));
   neptune_rt_ctx *c = new neptune_rt_ctx();
   c->device = device;
+  // any failure below releases what was built so far (neptune_rt_finalize tolerates a half-built ctx)
+#define INIT_CUDA(call)                                                                                     \
+  do {                                                                                                      \
+    cudaError_t e_ = (call);                                                                                \
+    if (e_ != cudaSuccess) {                                                                                \
+      neptune_rt_finalize(c);                                                                               \
+      return set_error(nullptr, NEPTUNE_RT_ECUDA, "%s failed: %s", #call, cudaGetErrorString(e_));          \
+    }                                                                                                       \
+  } while (0)
   cudaDeviceProp prop;
-  RT_CUDA(nullptr, cudaGetDeviceProperties(&prop, device));
+  INIT_CUDA(cudaGetDeviceProperties(&prop, device));
   c->sm_count = prop.multiProcessorCount;
   int lo = 0, hi = 0;
   cudaDeviceGetStreamPriorityRange(&lo, &hi);
-  RT_CUDA(nullptr, cudaStreamCreateWithPriority(&c->stream, cudaStreamNonBlocking, lo));
-  RT_CUDA(nullptr, cudaStreamCreateWithPriority(&c->halo_stream, cudaStreamNonBlocking, hi));
-  RT_CUDA(nullptr, cudaEventCreateWithFlags(&c->ev_boundary, cudaEventDisableTiming));
-  RT_CUDA(nullptr, cudaEventCreateWithFlags(&c->ev_halo, cudaEventDisableTiming));
-  RT_CUDA(nullptr, cudaEventCreate(&c->ev_t0));
-  RT_CUDA(nullptr, cudaEventCreate(&c->ev_t1));
-  RT_CUDA(nullptr, cudaStreamCreateWithFlags(&c->h2d_stream, cudaStreamNonBlocking));
-  RT_CUDA(nullptr, cudaStreamCreateWithFlags(&c->d2h_stream, cudaStreamNonBlocking));
+  INIT_CUDA(cudaStreamCreateWithPriority(&c->stream, cudaStreamNonBlocking, lo));
+  INIT_CUDA(cudaStreamCreateWithPriority(&c->halo_stream, cudaStreamNonBlocking, hi));
+  INIT_CUDA(cudaEventCreateWithFlags(&c->ev_boundary, cudaEventDisableTiming));
+  INIT_CUDA(cudaEventCreateWithFlags(&c->ev_halo, cudaEventDisableTiming));
+  INIT_CUDA(cudaEventCreate(&c->ev_t0));
+  INIT_CUDA(cudaEventCreate(&c->ev_t1));
+  INIT_CUDA(cudaStreamCreateWithFlags(&c->h2d_stream, cudaStreamNonBlocking));
+  INIT_CUDA(cudaStreamCreateWithFlags(&c->d2h_stream, cudaStreamNonBlocking));
+#undef INIT_CUDA
   *out = c;
   return NEPTUNE_RT_OK;
 }
@@ -322,22 +359,20 @@ extern "C" int neptune_rt_timer_stop(neptune_rt_ctx *c, double *ms) {
 extern "C" int neptune_rt_finalize(neptune_rt_ctx *c) {
   if (!c) return NEPTUNE_RT_OK;
   cudaSetDevice(c->device);
-  cudaStreamSynchronize(c->stream);
-  cudaStreamSynchronize(c->halo_stream);
+  for (cudaStream_t st : {c->stream, c->halo_stream, c->h2d_stream, c->d2h_stream})
+    if (st) cudaStreamSynchronize(st);
   if (c->comm && nccl().ok) nccl().CommDestroy(c->comm);
-  cudaEventDestroy(c->ev_boundary);
-  cudaEventDestroy(c->ev_halo);
-  cudaEventDestroy(c->ev_t0);
-  cudaEventDestroy(c->ev_t1);
-  cudaStreamDestroy(c->stream);
-  cudaStreamDestroy(c->halo_stream);
-  cudaStreamSynchronize(c->h2d_stream);
-  cudaStreamSynchronize(c->d2h_stream);
-  cudaStreamDestroy(c->h2d_stream);
-  cudaStreamDestroy(c->d2h_stream);
+  for (cudaEvent_t e : {c->ev_boundary, c->ev_halo, c->ev_t0, c->ev_t1})
+    if (e) cudaEventDestroy(e);
+  for (cudaStream_t st : {c->stream, c->halo_stream, c->h2d_stream, c->d2h_stream})
+    if (st) cudaStreamDestroy(st);
   for (cudaEvent_t e : c->ev_pool) cudaEventDestroy(e);
+  for (cudaEvent_t e : c->trace_events) cudaEventDestroy(e);
   if (c->red_partials) cudaFree(c->red_partials);
   if (c->red_host) cudaFreeHost(c->red_host);
+  if (c->agree_dev) cudaFree(c->agree_dev);
+  if (c->agree_host) cudaFreeHost(c->agree_host);
+  for (auto &fn : c->on_finalize) fn();
   delete c;
   return NEPTUNE_RT_OK;
 }
@@ -388,7 +423,9 @@ extern "C" int neptune_rt_field_alloc(neptune_rt_ctx *c, int dtype, int rank, co
 extern "C" int neptune_rt_field_free(neptune_rt_field *f) {
   if (!f) return NEPTUNE_RT_OK;
   cudaSetDevice(f->ctx->device);
-  cudaStreamSynchronize(f->ctx->stream);
+  // the halo, upload and download streams may still be reading or writing this field
+  for (cudaStream_t st : {f->ctx->halo_stream, f->ctx->h2d_stream, f->ctx->stream, f->ctx->d2h_stream})
+    if (st) cudaStreamSynchronize(st);
   if (f->owned) cudaFree(f->dptr);
   delete f;
   return NEPTUNE_RT_OK;
@@ -612,8 +649,11 @@ extern "C" int neptune_rt_stencil_set(neptune_rt_stencil *s, const char *key, co
   if (k == "zchunk") { s->zchunk = std::max(0, std::atoi(value)); return NEPTUNE_RT_OK; }
   if (k == "tblock") {
     const int t = std::atoi(value);
-    if (t < 0 || t > 2) return set_error(s->ctx, NEPTUNE_RT_EINVAL, "stencil_set: tblock must be 0 (auto), 1 or 2");
-    s->tblock = t;
+    // 4 and 8 are depths of the communication-avoiding block in slab mode (one exchange of tblock * radius ghost planes
+    // per tblock steps, set up with neptune_rt_slab_localize(halo = tblock * radius)); a launch still fuses two steps
+    if (t != 0 && t != 1 && t != 2 && t != 4 && t != 8)
+      return set_error(s->ctx, NEPTUNE_RT_EINVAL, "stencil_set: tblock must be 0 (auto), 1, 2, 4 or 8");
+    s->tblock = t > 2 ? 2 : t;
     return NEPTUNE_RT_OK;
   }
   if (k == "fma") { s->fma = v == "1" || v == "true"; return NEPTUNE_RT_OK; }
@@ -735,8 +775,10 @@ int do_apply(neptune_rt_stencil *s, int n_in, neptune_rt_field *const *in, neptu
     for (int x = 0; x < d.rank; ++x)
       if (f->lb[x] != d.in_lb[(size_t)k * d.rank + x] || f->ub[x] != d.in_ub[(size_t)k * d.rank + x])
         return set_error(c, NEPTUNE_RT_EINVAL, "neptune_rt_apply: input %d bounds differ from the apply's operand type", k);
-    if (f->dptr == out->dptr)
-      return set_error(c, NEPTUNE_RT_EINVAL, "neptune_rt_apply: the result aliases input %d (the reference allocates a fresh result, DataflowLowering.cpp:273-281)", k);
+    // byte ranges, not pointer equality: wrapped fields may be overlapping views of one work vector
+    const char *ib = (const char *)f->dptr, *ob = (const char *)out->dptr;
+    if (ib < ob + out->bytes && ob < ib + f->bytes)
+      return set_error(c, NEPTUNE_RT_EINVAL, "neptune_rt_apply: the result overlaps input %d in memory (the reference allocates a fresh result, DataflowLowering.cpp:273-281)", k);
   }
   const int cd0 = 3 - d.rank;
   if (p0 < 0 || p1 > out->ext[cd0] || p0 > p1) return set_error(c, NEPTUNE_RT_EINVAL, "neptune_rt_apply_planes: plane range [%lld, %lld)", (long long)p0, (long long)p1);
@@ -773,7 +815,7 @@ int do_apply(neptune_rt_stencil *s, int n_in, neptune_rt_field *const *in, neptu
     a.wlo[x] = 0;
     a.whi[x] = (int)out->ext[x];
   }
-  if (two_steps && s->slab_set) {
+  if ((two_steps || s->slab_loop) && s->slab_set) {
     // level-1 planes next to the owned slab lie on ghost planes: test them against the GLOBAL apply
     // bounds (clipped to the local box), not the owned-plane intersection the local descriptor carries
     a.blo[cd0] = (int)(std::max(s->slab_glb0, d.out_lb[0]) - d.out_lb[0]);
@@ -899,6 +941,7 @@ extern "C" int neptune_rt_apply_planes(neptune_rt_stencil *s, int n_in, neptune_
 extern "C" int neptune_rt_apply_host(neptune_rt_stencil *s, int n_in, neptune_rt_field *const *in, const void *const *in_host,
                                      neptune_rt_field *out, void *out_host, int64_t chunk_planes) {
   if (!s || !in || !in_host || !out || !out_host) return set_error(s ? s->ctx : nullptr, NEPTUNE_RT_EINVAL, "neptune_rt_apply_host: NULL argument");
+  NvtxRange nvtx_range("neptune_rt_apply_host");
   neptune_rt_ctx *c = s->ctx;
   const neptune_rt_stencil_desc &d = s->desc.c;
   if (n_in != d.n_inputs) return set_error(c, NEPTUNE_RT_EINVAL, "neptune_rt_apply_host: %d inputs given, the apply has %d", n_in, d.n_inputs);
@@ -1031,6 +1074,25 @@ extern "C" int neptune_rt_comm_init(neptune_rt_ctx *c, const void *id128, int nr
   RT_NCCL(c, nccl().CommInitRank(&c->comm, nranks, id, rank));
   c->nranks = nranks;
   c->rank = rank;
+  // NCCL sets up its peer-to-peer channels on first use: do one throw-away neighbour exchange of a halo-sized
+  // message now, so that the first timed exchange does not pay for connection set-up
+  if (nranks > 1) {
+    const size_t W = (size_t)4 << 20;
+    char *buf = nullptr;
+    RT_CUDA(c, cudaMalloc(&buf, 4 * W));
+    RT_NCCL(c, nccl().GroupStart());
+    if (rank > 0) {
+      RT_NCCL(c, nccl().Send(buf, W, ncclChar, rank - 1, c->comm, c->halo_stream));
+      RT_NCCL(c, nccl().Recv(buf + W, W, ncclChar, rank - 1, c->comm, c->halo_stream));
+    }
+    if (rank + 1 < nranks) {
+      RT_NCCL(c, nccl().Send(buf + 2 * W, W, ncclChar, rank + 1, c->comm, c->halo_stream));
+      RT_NCCL(c, nccl().Recv(buf + 3 * W, W, ncclChar, rank + 1, c->comm, c->halo_stream));
+    }
+    RT_NCCL(c, nccl().GroupEnd());
+    RT_CUDA(c, cudaStreamSynchronize(c->halo_stream));
+    RT_CUDA(c, cudaFree(buf));
+  }
   return NEPTUNE_RT_OK;
 }
 
@@ -1068,6 +1130,7 @@ extern "C" int neptune_rt_halo_exchange(neptune_rt_ctx *c, neptune_rt_field *f, 
 extern "C" int neptune_rt_run_steps(neptune_rt_stencil *s, neptune_rt_field *fa, neptune_rt_field *fb, int n_extra,
                                     neptune_rt_field *const *extra, int64_t nsteps, neptune_rt_field **result) {
   if (!s || !fa || !fb) return set_error(s ? s->ctx : nullptr, NEPTUNE_RT_EINVAL, "run_steps: NULL argument");
+  NvtxRange nvtx_range("neptune_rt_run_steps");
   neptune_rt_ctx *c = s->ctx;
   const neptune_rt_stencil_desc &d = s->desc.c;
   if (n_extra != d.n_inputs - 1) return set_error(c, NEPTUNE_RT_EINVAL, "run_steps: %d extra inputs given, the apply has %d", n_extra, d.n_inputs - 1);
@@ -1096,68 +1159,180 @@ extern "C" int neptune_rt_run_steps(neptune_rt_stencil *s, neptune_rt_field *fa,
 
   // slab mode: the local box is [own - ghost, own + ghost) clipped to the global box, as built by
   // neptune_rt_slab_localize; ghost planes exist on the sides that have a neighbour.  A launch that
-  // fuses T steps (T = 1, or 2 with temporal blocking) needs T*radius valid ghost planes going in
-  // and refreshes as many coming out: first the T*radius owned planes next to each neighbour, whose
-  // exchange then overlaps the interior launch.
+  // advances T steps (T = 1, or 2 with temporal blocking) consumes T*radius valid ghost planes.  With G
+  // ghost planes a rank goes G / (T*radius) launches between exchanges: launch i of such a cycle also
+  // computes the ghost planes that are still valid afterwards (redundantly with the neighbour, bit for
+  // bit the same arithmetic), the last launch of the cycle computes its G owned boundary planes first
+  // and their exchange overlaps the interior launch.  G = T*radius is the classic one-exchange-per-launch
+  // scheme; deeper ghosts trade a few redundant planes for fewer thin boundary launches and exchanges.
   int64_t radius = 0;
   for (int i = 0; i < d.n_ops; ++i)
     if (d.ops[i].opcode == NEPTUNE_RT_OP_ACCESS) radius = std::max<int64_t>(radius, std::llabs(d.ops[i].offset[0]));
   const int64_t ghost = s->slab_set ? s->slab_ghost : radius;
+  // (ghost and radius are the same on every rank: this error is raised by all of them together)
   if (ghost < radius) return set_error(c, NEPTUNE_RT_EINVAL, "run_steps: %lld ghost planes are fewer than the dim-0 stencil radius", (long long)ghost);
   const bool up = c->rank > 0, down = c->rank + 1 < c->nranks;
   const int64_t own_b = up ? ghost : 0, own_e = n0 - (down ? ghost : 0);
-  if (own_e - own_b < 2 * ghost) return set_error(c, NEPTUNE_RT_EINVAL, "run_steps: slab of %lld planes is thinner than two halos", (long long)(own_e - own_b));
-  const bool fuse2 = s->tblock != 1 && ghost >= 2 * radius && own_e - own_b >= 4 * radius && tb2_eligible(s, cur, nxt, true, n_extra, extra);
+
+  // Facts that can differ between ranks (slab thickness when n0 % nranks != 0, alignment of wrapped device
+  // memory, ...) must not steer the exchange pattern locally: a rank that took another branch would leave
+  // its neighbour blocked in ncclRecv.  They are agreed once per (fields, settings) with one ncclAllReduce(min).
+  {
+    neptune_rt_stencil::Agreed &ag = s->agreed;
+    bool same = ag.valid && ag.tblock == s->tblock && ag.want_tb == s->want_tb && (int)ag.extra.size() == n_extra &&
+                ((ag.a == fa && ag.b == fb) || (ag.a == fb && ag.b == fa));
+    for (int k = 0; same && k < n_extra; ++k) same = ag.extra[(size_t)k] == extra[k];
+    if (!same) {
+      int local[4];
+      local[0] = (s->tblock != 1 && ghost >= 2 * radius && own_e - own_b >= 4 * radius && tb2_eligible(s, cur, nxt, true, n_extra, extra)) ? 1 : 0;
+      local[1] = own_e - own_b >= 2 * ghost ? 1 : 0;    // boundary planes and interior can be split
+      local[2] = own_e - own_b >= ghost ? 1 : 0;        // the owned planes cover a whole halo
+      local[3] = 1;
+      cudaSetDevice(c->device);
+      if (!c->agree_dev) {
+        RT_CUDA(c, cudaMalloc(&c->agree_dev, 4 * sizeof(int)));
+        RT_CUDA(c, cudaMallocHost(&c->agree_host, 4 * sizeof(int)));
+      }
+      std::memcpy(c->agree_host, local, sizeof local);
+      RT_CUDA(c, cudaMemcpyAsync(c->agree_dev, c->agree_host, sizeof local, cudaMemcpyHostToDevice, c->stream));
+      RT_NCCL(c, nccl().AllReduce(c->agree_dev, c->agree_dev, 4, ncclInt, ncclMin, c->comm, c->stream));
+      RT_CUDA(c, cudaMemcpyAsync(c->agree_host, c->agree_dev, sizeof local, cudaMemcpyDeviceToHost, c->stream));
+      RT_CUDA(c, cudaStreamSynchronize(c->stream));
+      if (!c->agree_host[2])
+        return set_error(c, NEPTUNE_RT_EINVAL, "run_steps: some rank's slab is thinner than the %lld ghost planes it must send (this rank owns %lld planes)",
+                         (long long)ghost, (long long)(own_e - own_b));
+      ag.valid = true;
+      ag.fuse2 = c->agree_host[0] != 0;
+      ag.split = c->agree_host[1] != 0;
+      ag.a = fa; ag.b = fb;
+      ag.extra.assign(extra, extra + n_extra);
+      ag.tblock = s->tblock;
+      ag.want_tb = s->want_tb;
+    }
+  }
+  const bool fuse2 = s->agreed.fuse2, split = s->agreed.split;
+
+  struct LoopGuard {   // dim-0 bounds of every launch below are the global apply bounds (ghost planes are computed too)
+    neptune_rt_stencil *s;
+    ~LoopGuard() { s->slab_loop = false; }
+  } guard{s};
+  s->slab_loop = true;
+
+  // trace: four timing events per launch group
+  const bool trace = c->trace_on;
+  if (trace) { c->trace_groups = 0; c->trace_kind.clear(); }
+  auto trace_mark = [&](int which, cudaStream_t st) -> int {
+    if (!trace) return NEPTUNE_RT_OK;
+    const size_t idx = (size_t)c->trace_groups * 4 + (size_t)which;
+    while (c->trace_events.size() <= idx) {
+      cudaEvent_t e;
+      RT_CUDA(c, cudaEventCreate(&e));
+      c->trace_events.push_back(e);
+    }
+    RT_CUDA(c, cudaEventRecord(c->trace_events[idx], st));
+    return NEPTUNE_RT_OK;
+  };
+  auto nccl_health = [&]() -> int {   // a dead peer must become an error, not a hung cudaStreamSynchronize
+    if (!nccl().CommGetAsyncError) return NEPTUNE_RT_OK;
+    ncclResult_t st = ncclSuccess;
+    if (nccl().CommGetAsyncError(c->comm, &st) != ncclSuccess || (st != ncclSuccess && st != ncclInProgress))
+      return set_error(c, NEPTUNE_RT_ENCCL, "NCCL reported an asynchronous error in the halo exchange: %s", nccl().GetErrorString(st));
+    return NEPTUNE_RT_OK;
+  };
+
   // every ghost plane of the first input state
   RT_CUDA(c, cudaEventRecord(c->ev_boundary, c->stream));
   RT_CUDA(c, cudaStreamWaitEvent(c->halo_stream, c->ev_boundary, 0));
   if (int rc = neptune_rt_halo_exchange(c, cur, own_b, own_e, ghost, c->halo_stream)) return rc;
-  // a fused pair of steps evaluates level 1 on the first ghost plane, which reads the pointwise
-  // inputs there: bring their ghost planes up to date once (they do not change over the time loop)
-  if (fuse2)
+  // launches that compute ghost planes read the other inputs (coefficients, right-hand side) there:
+  // bring their ghost planes up to date once (they do not change over the time loop)
+  if (ghost > radius || fuse2)
     for (int k = 0; k < n_extra; ++k)
       if (int rc = neptune_rt_halo_exchange(c, extra[k], own_b, own_e, ghost, c->halo_stream)) return rc;
   RT_CUDA(c, cudaEventRecord(c->ev_halo, c->halo_stream));
   RT_CUDA(c, cudaStreamWaitEvent(c->stream, c->ev_halo, 0));
-  const char *sb_env = std::getenv("NEPTUNE_RT_SLAB_BOUNDARY_STREAM");
-  const bool side_boundary = sb_env && sb_env[0] == '1';
+  int64_t valid = ghost;   // ghost planes of `cur` that hold the neighbour's current state
   for (int64_t t = 0; t < nsteps;) {
     const bool two = fuse2 && t + 2 <= nsteps;
-    const int64_t w = two ? 2 * radius : radius;  // planes computed first and exchanged
+    const int64_t adv = two ? 2 * radius : radius;          // ghost planes this launch consumes
+    const int64_t left = nsteps - t - (two ? 2 : 1);        // steps after this launch
+    const int64_t adv_next = (fuse2 && left >= 2) ? 2 * radius : radius;
+    const bool exchange = left > 0 && valid - adv < adv_next;
     ins[0] = cur;
-    // 1. boundary planes of the owned slab, so their exchange can start early
-    // NEPTUNE_RT_SLAB_BOUNDARY_STREAM=1 (experimental): the boundary launch goes to the high-priority
-    // stream, beside the interior (they write disjoint planes) instead of ahead of it
-    cudaStream_t bstream = c->stream;
-    if (side_boundary) {
+    if (int rc = trace_mark(0, c->stream)) return rc;
+    if (!exchange) {
+      // one launch over the owned planes plus the ghost planes that stay valid
+      const int64_t ext = left > 0 ? valid - adv : 0;
+      if (int rc = do_apply(s, d.n_inputs, ins, nxt, own_b - (up ? ext : 0), own_e + (down ? ext : 0), c->stream, two)) return rc;
+      valid -= adv;
+      if (trace) { for (int w = 1; w < 4; ++w) if (int rc = trace_mark(w, c->stream)) return rc; }
+    } else if (!split) {
+      // thin slab (agreed by all ranks): sweep, then exchange, not overlapped
+      if (int rc = do_apply(s, d.n_inputs, ins, nxt, own_b, own_e, c->stream, two)) return rc;
+      if (int rc = trace_mark(1, c->stream)) return rc;
       RT_CUDA(c, cudaEventRecord(c->ev_boundary, c->stream));
       RT_CUDA(c, cudaStreamWaitEvent(c->halo_stream, c->ev_boundary, 0));
-      bstream = c->halo_stream;
-    }
-    if (w > 0) {
+      if (int rc = neptune_rt_halo_exchange(c, nxt, own_b, own_e, ghost, c->halo_stream)) return rc;
+      if (int rc = trace_mark(2, c->halo_stream)) return rc;
+      RT_CUDA(c, cudaEventRecord(c->ev_halo, c->halo_stream));
+      RT_CUDA(c, cudaStreamWaitEvent(c->stream, c->ev_halo, 0));
+      if (int rc = trace_mark(3, c->stream)) return rc;
+      valid = ghost;
+    } else {
+      // 1. the `ghost` owned planes next to each neighbour, so that their exchange can start early
+      const int64_t w = ghost;
       if (up && down && own_b + w < own_e - w) {   // both sides in one launch (two plane ranges)
-        if (int rc = do_apply(s, d.n_inputs, ins, nxt, own_b, own_e, bstream, two, own_b + w, own_e - w)) return rc;
+        if (int rc = do_apply(s, d.n_inputs, ins, nxt, own_b, own_e, c->stream, two, own_b + w, own_e - w)) return rc;
       } else {
-        if (up) if (int rc = do_apply(s, d.n_inputs, ins, nxt, own_b, own_b + w, bstream, two)) return rc;
-        if (down) if (int rc = do_apply(s, d.n_inputs, ins, nxt, own_e - w, own_e, bstream, two)) return rc;
+        if (up) if (int rc = do_apply(s, d.n_inputs, ins, nxt, own_b, own_b + w, c->stream, two)) return rc;
+        if (down) if (int rc = do_apply(s, d.n_inputs, ins, nxt, own_e - w, own_e, c->stream, two)) return rc;
       }
-    }
-    if (!side_boundary) {
+      if (int rc = trace_mark(1, c->stream)) return rc;
       RT_CUDA(c, cudaEventRecord(c->ev_boundary, c->stream));
       RT_CUDA(c, cudaStreamWaitEvent(c->halo_stream, c->ev_boundary, 0));
+      // 2. halo exchange of the new state on the high-priority stream, concurrent with 3.
+      if (int rc = neptune_rt_halo_exchange(c, nxt, own_b, own_e, w, c->halo_stream)) return rc;
+      if (int rc = trace_mark(2, c->halo_stream)) return rc;
+      RT_CUDA(c, cudaEventRecord(c->ev_halo, c->halo_stream));
+      // 3. interior
+      if (int rc = do_apply(s, d.n_inputs, ins, nxt, own_b + (up ? w : 0), own_e - (down ? w : 0), c->stream, two)) return rc;
+      if (int rc = trace_mark(3, c->stream)) return rc;
+      // 4. join
+      RT_CUDA(c, cudaStreamWaitEvent(c->stream, c->ev_halo, 0));
+      valid = ghost;
     }
-    // 2. halo exchange of the new state on the high-priority stream, concurrent with 3.
-    if (int rc = neptune_rt_halo_exchange(c, nxt, own_b, own_e, w, c->halo_stream)) return rc;
-    RT_CUDA(c, cudaEventRecord(c->ev_halo, c->halo_stream));
-    // 3. interior
-    if (int rc = do_apply(s, d.n_inputs, ins, nxt, own_b + (up ? w : 0), own_e - (down ? w : 0), c->stream, two)) return rc;
-    // 4. join
-    RT_CUDA(c, cudaStreamWaitEvent(c->stream, c->ev_halo, 0));
+    if (trace) { c->trace_kind.push_back((two ? 20 : 10) + (exchange ? 1 : 0)); c->trace_groups++; }
+    if (exchange) if (int rc = nccl_health()) return rc;
     std::swap(cur, nxt);
     t += two ? 2 : 1;
   }
   if (result) *result = cur;
   return NEPTUNE_RT_OK;
+}
+
+// Per-launch-group timestamps of the slab time loop (milliseconds since the first group began): begin, boundary
+// planes done, exchange done, interior done.  Enable, run neptune_rt_run_steps, read.  Costs four event records per group.
+extern "C" int neptune_rt_slab_trace(neptune_rt_ctx *c, int enable) {
+  if (!c) return set_error(nullptr, NEPTUNE_RT_EINVAL, "slab_trace: NULL ctx");
+  c->trace_on = enable != 0;
+  return NEPTUNE_RT_OK;
+}
+extern "C" int neptune_rt_slab_trace_read(neptune_rt_ctx *c, double *out, int capacity_groups, int *kinds) {
+  if (!c) return 0;
+  cudaSetDevice(c->device);
+  const int n = std::min(c->trace_groups, capacity_groups);
+  if (c->trace_groups == 0 || !out) return c->trace_groups;
+  cudaStreamSynchronize(c->stream);
+  cudaStreamSynchronize(c->halo_stream);
+  for (int g = 0; g < n; ++g) {
+    for (int w = 0; w < 4; ++w) {
+      float ms = 0;
+      cudaEventElapsedTime(&ms, c->trace_events[0], c->trace_events[(size_t)g * 4 + (size_t)w]);
+      out[g * 4 + w] = ms;
+    }
+    if (kinds) kinds[g] = c->trace_kind[(size_t)g];
+  }
+  return c->trace_groups;
 }
 
 extern "C" int neptune_rt_stencil_set_slab(neptune_rt_stencil *s, int64_t ghost, int64_t global_lb0, int64_t global_ub0) {
@@ -1181,26 +1356,126 @@ static neptune_rt_ctx *default_ctx() {
   return ctx;
 }
 
-extern "C" void neptune_rt_apply_memref(const neptune_rt_stencil_desc *d, int n_in, const void *const *in_host, void *out_host) {
-  neptune_rt_ctx *c = default_ctx();
-  auto die = [&](const char *what) {
-    std::fprintf(stderr, "[NeptuneRT-B200] %s: %s\n", what, neptune_rt_last_error(c));
-    std::abort();  // generated code does not check statuses (NeptunePETScRuntime.cpp:15-30)
-  };
-  if (!d || !in_host || !out_host || n_in != d->n_inputs) { set_error(c, NEPTUNE_RT_EINVAL, "bad arguments"); die("neptune_rt_apply_memref"); }
-  neptune_rt_stencil *s = nullptr;
-  if (neptune_rt_stencil_create(c, d, &s)) die("neptune_rt_stencil_create");
-  std::vector<neptune_rt_field *> ins(n_in, nullptr);
-  for (int k = 0; k < n_in; ++k) {
-    if (neptune_rt_field_alloc(c, d->dtype, d->rank, d->in_lb + (size_t)k * d->rank, d->in_ub + (size_t)k * d->rank, &ins[k])) die("neptune_rt_field_alloc");
-    if (neptune_rt_field_upload(ins[k], in_host[k])) die("neptune_rt_field_upload");
-  }
+// What generated code calls (include/neptune_rt.h): MLIR memref descriptors in, one sweep, result in the output
+// memref.  The stencil and the device fields are created on first use and cached by the descriptor's content
+// (body, constants, bounds), so a host time loop that calls this once per step pays one pipelined
+// upload | sweep | download (neptune_rt_apply_host) per call and no allocation.  Failures abort, as the reference's
+// shims do (NeptunePETScRuntime.cpp:15-30): generated code does not check statuses.
+namespace {
+
+struct MemrefCacheEntry {
+  uint64_t digest = 0;
+  neptune_rt_stencil *stencil = nullptr;
+  std::vector<neptune_rt_field *> in;
   neptune_rt_field *out = nullptr;
-  if (neptune_rt_field_alloc(c, d->dtype, d->rank, d->out_lb, d->out_ub, &out)) die("neptune_rt_field_alloc");
-  if (neptune_rt_apply(s, n_in, ins.data(), out)) die("neptune_rt_apply");
-  if (neptune_rt_field_download(out, out_host)) die("neptune_rt_field_download");
-  if (neptune_rt_sync(c)) die("neptune_rt_sync");
-  for (auto *f : ins) neptune_rt_field_free(f);
-  neptune_rt_field_free(out);
-  neptune_rt_stencil_destroy(s);
+};
+std::vector<MemrefCacheEntry> &memref_cache() {
+  static std::vector<MemrefCacheEntry> v;
+  return v;
+}
+
+uint64_t fnv(uint64_t h, const void *p, size_t n) {
+  const unsigned char *b = (const unsigned char *)p;
+  for (size_t i = 0; i < n; ++i) { h ^= b[i]; h *= 1099511628211ull; }
+  return h;
+}
+
+uint64_t desc_digest(const neptune_rt_stencil_desc &d) {
+  uint64_t h = 1469598103934665603ull;
+  h = fnv(h, &d.rank, sizeof d.rank); h = fnv(h, &d.dtype, sizeof d.dtype);
+  h = fnv(h, &d.n_inputs, sizeof d.n_inputs); h = fnv(h, &d.yield_value, sizeof d.yield_value);
+  h = fnv(h, &d.flags, sizeof d.flags);
+  for (int i = 0; i < d.n_ops; ++i) {
+    const neptune_rt_body_op &o = d.ops[i];
+    h = fnv(h, &o.opcode, sizeof o.opcode); h = fnv(h, &o.a, sizeof o.a); h = fnv(h, &o.b, sizeof o.b);
+    h = fnv(h, &o.input, sizeof o.input); h = fnv(h, o.offset, sizeof o.offset); h = fnv(h, &o.value, sizeof o.value);
+  }
+  h = fnv(h, d.lb, sizeof(int64_t) * d.rank); h = fnv(h, d.ub, sizeof(int64_t) * d.rank);
+  h = fnv(h, d.out_lb, sizeof(int64_t) * d.rank); h = fnv(h, d.out_ub, sizeof(int64_t) * d.rank);
+  h = fnv(h, d.in_lb, sizeof(int64_t) * (size_t)d.rank * d.n_inputs);
+  h = fnv(h, d.in_ub, sizeof(int64_t) * (size_t)d.rank * d.n_inputs);
+  return h;
+}
+
+[[noreturn]] void memref_die(neptune_rt_ctx *c, const char *what) {
+  std::fprintf(stderr, "[NeptuneRT-B200] %s: %s\n", what, neptune_rt_last_error(c));
+  std::abort();  // generated code does not check statuses (NeptunePETScRuntime.cpp:15-30)
+}
+
+// host pointers of contiguous row-major boxes -> one cached, pipelined sweep
+void apply_memref_ptrs(const neptune_rt_stencil_desc *d, int n_in, const void *const *in_host, void *out_host) {
+  neptune_rt_ctx *c = default_ctx();
+  if (!d || !in_host || !out_host || n_in != d->n_inputs) { set_error(c, NEPTUNE_RT_EINVAL, "bad arguments"); memref_die(c, "neptune_rt_apply_memref"); }
+  NvtxRange nvtx_range("neptune_rt_apply_memref");
+  const uint64_t dg = desc_digest(*d);
+  MemrefCacheEntry *e = nullptr;
+  for (auto &x : memref_cache()) if (x.digest == dg) { e = &x; break; }
+  if (!e) {
+    MemrefCacheEntry n;
+    n.digest = dg;
+    if (neptune_rt_stencil_create(c, d, &n.stencil)) memref_die(c, "neptune_rt_stencil_create");
+    n.in.assign((size_t)n_in, nullptr);
+    for (int k = 0; k < n_in; ++k)
+      if (neptune_rt_field_alloc(c, d->dtype, d->rank, d->in_lb + (size_t)k * d->rank, d->in_ub + (size_t)k * d->rank, &n.in[(size_t)k])) memref_die(c, "neptune_rt_field_alloc");
+    if (neptune_rt_field_alloc(c, d->dtype, d->rank, d->out_lb, d->out_ub, &n.out)) memref_die(c, "neptune_rt_field_alloc");
+    memref_cache().push_back(n);
+    e = &memref_cache().back();
+  }
+  if (neptune_rt_apply_host(e->stencil, n_in, e->in.data(), in_host, e->out, out_host, 0)) memref_die(c, "neptune_rt_apply_host");
+}
+
+// MLIR memref descriptor (allocated, aligned, offset, sizes[R], strides[R]) -> host pointer of a contiguous row-major box
+template <int R, class M> const void *memref_host_ptr(neptune_rt_ctx *c, const M &m, int dtype, const int64_t *lb, const int64_t *ub, const char *what) {
+  int64_t expect = 1;
+  for (int x = R - 1; x >= 0; --x) {
+    if (m.sizes[x] != ub[x] - lb[x]) {
+      set_error(c, NEPTUNE_RT_EINVAL, "%s: memref size %lld in dim %d, the apply's type says %lld", what, (long long)m.sizes[x], x, (long long)(ub[x] - lb[x]));
+      memref_die(c, "neptune_rt_apply_memref");
+    }
+    if (m.sizes[x] > 1 && m.strides[x] != expect) {
+      set_error(c, NEPTUNE_RT_EUNSUPPORTED, "%s: stride %lld in dim %d is not the identity layout (%lld); strided memrefs are not on the B200 path", what,
+                (long long)m.strides[x], x, (long long)expect);
+      memref_die(c, "neptune_rt_apply_memref");
+    }
+    expect *= m.sizes[x];
+  }
+  if (!m.aligned) { set_error(c, NEPTUNE_RT_EINVAL, "%s: NULL aligned pointer", what); memref_die(c, "neptune_rt_apply_memref"); }
+  const size_t S = dtype == NEPTUNE_RT_F64 ? 8 : 4;
+  return (const char *)m.aligned + (size_t)m.offset * S;
+}
+
+template <int R, class M> void apply_memref_rank(const neptune_rt_stencil_desc *d, int n_in, const M *in, const M *out) {
+  neptune_rt_ctx *c = default_ctx();
+  if (!d || !in || !out || d->rank != R || n_in != d->n_inputs || n_in > NEPTUNE_RT_MAX_INPUTS) {
+    set_error(c, NEPTUNE_RT_EINVAL, "descriptor rank / input count do not match the call (rank %d, %d inputs)", R, n_in);
+    memref_die(c, "neptune_rt_apply_memref");
+  }
+  const void *hp[NEPTUNE_RT_MAX_INPUTS];
+  for (int k = 0; k < n_in; ++k)
+    hp[k] = memref_host_ptr<R>(c, in[k], d->dtype, d->in_lb + (size_t)k * R, d->in_ub + (size_t)k * R, "input memref");
+  void *op = const_cast<void *>(memref_host_ptr<R>(c, *out, d->dtype, d->out_lb, d->out_ub, "result memref"));
+  apply_memref_ptrs(d, n_in, hp, op);
+}
+
+}  // namespace
+
+extern "C" void neptune_rt_apply_memref_1d(const neptune_rt_stencil_desc *d, int n_in, const neptune_rt_memref_1d *in, const neptune_rt_memref_1d *out) {
+  apply_memref_rank<1>(d, n_in, in, out);
+}
+extern "C" void neptune_rt_apply_memref_2d(const neptune_rt_stencil_desc *d, int n_in, const neptune_rt_memref_2d *in, const neptune_rt_memref_2d *out) {
+  apply_memref_rank<2>(d, n_in, in, out);
+}
+extern "C" void neptune_rt_apply_memref_3d(const neptune_rt_stencil_desc *d, int n_in, const neptune_rt_memref_3d *in, const neptune_rt_memref_3d *out) {
+  apply_memref_rank<3>(d, n_in, in, out);
+}
+extern "C" void neptune_rt_apply_memref(const neptune_rt_stencil_desc *d, int n_in, const void *const *in_host, void *out_host) {
+  apply_memref_ptrs(d, n_in, in_host, out_host);
+}
+extern "C" void neptune_rt_memref_cache_clear(void) {
+  for (auto &e : memref_cache()) {
+    for (auto *f : e.in) neptune_rt_field_free(f);
+    neptune_rt_field_free(e.out);
+    neptune_rt_stencil_destroy(e.stencil);
+  }
+  memref_cache().clear();
 }

@@ -107,7 +107,13 @@ def lib() -> C.CDLL:
         "neptune_rt_comm_unique_id": (i32, [vp]),
         "neptune_rt_comm_init": (i32, [vp, vp, i32, i32]),
         "neptune_rt_halo_exchange": (i32, [vp, vp, i64, i64, i64, vp]),
+        "neptune_rt_slab_trace": (i32, [vp, i32]),
+        "neptune_rt_slab_trace_read": (i32, [vp, C.POINTER(C.c_double), i32, C.POINTER(i32)]),
         "neptune_rt_apply_memref": (None, [C.POINTER(StencilDescC), i32, C.POINTER(vp), vp]),
+        "neptune_rt_apply_memref_1d": (None, [C.POINTER(StencilDescC), i32, vp, vp]),
+        "neptune_rt_apply_memref_2d": (None, [C.POINTER(StencilDescC), i32, vp, vp]),
+        "neptune_rt_apply_memref_3d": (None, [C.POINTER(StencilDescC), i32, vp, vp]),
+        "neptune_rt_memref_cache_clear": (None, []),
         "neptune_b200_compile": (i32, [C.c_char_p, C.c_char_p, C.POINTER(vp), C.c_char_p, C.c_size_t]),
         "neptune_b200_module_destroy": (i32, [vp]),
         "neptune_b200_apply_count": (i32, [vp]),
@@ -117,6 +123,9 @@ def lib() -> C.CDLL:
         "neptune_b200_function_arg_count": (i32, [vp, C.c_char_p]),
         "neptune_b200_function_arg_numel": (i64, [vp, C.c_char_p, i32]),
         "neptune_b200_last_error": (C.c_char_p, [vp]),
+        "neptune_b200_function_count": (i32, [vp]),
+        "neptune_b200_function_name": (C.c_char_p, [vp, i32]),
+        "neptune_b200_function_diagnostic": (C.c_char_p, [vp, C.c_char_p]),
         "neptune_b200_apply_stencil": (vp, [vp, vp, i32]),
         "neptune_b200_apply_cuda_source": (C.c_char_p, [vp, i32]),
         "neptune_b200_run_host": (i32, [vp, vp, C.c_char_p, i32, C.POINTER(vp)]),
@@ -251,6 +260,18 @@ class Context:
         ms = C.c_double()
         self._check(self._L.neptune_rt_timer_stop(self.h, C.byref(ms)))
         return ms.value
+
+    def slab_trace(self, enable: bool = True):
+        self._check(self._L.neptune_rt_slab_trace(self.h, int(enable)))
+
+    def slab_trace_read(self):
+        """[(kind, begin_ms, boundary_done_ms, exchange_done_ms, interior_done_ms)] of the last traced run_steps."""
+        n = self._L.neptune_rt_slab_trace_read(self.h, None, 0, None)
+        if n <= 0:
+            return []
+        buf, kinds = (C.c_double * (4 * n))(), (C.c_int * n)()
+        self._L.neptune_rt_slab_trace_read(self.h, buf, n, kinds)
+        return [(kinds[g],) + tuple(buf[4 * g + w] for w in range(4)) for g in range(n)]
 
     def comm_init(self, unique_id: bytes, nranks: int, rank: int):
         self._check(self._L.neptune_rt_comm_init(self.h, C.c_char_p(unique_id), nranks, rank))
@@ -455,6 +476,14 @@ class Module:
         if p is None:
             raise KeyError(function)
         return p.decode()
+
+    def functions(self) -> List[str]:
+        return [self._L.neptune_b200_function_name(self.h, i).decode() for i in range(self._L.neptune_b200_function_count(self.h))]
+
+    def diagnostic(self, function: str) -> Optional[str]:
+        """Why `function` was not lowered (None: it was)."""
+        p = self._L.neptune_b200_function_diagnostic(self.h, function.encode())
+        return None if p is None else p.decode()
 
     def arg_count(self, function: str = "@entry") -> int:
         return self._L.neptune_b200_function_arg_count(self.h, function.encode())

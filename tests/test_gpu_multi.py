@@ -20,7 +20,7 @@ def _free_port():
     return p
 
 
-def _worker(rank, world, port, name, shape, steps, q, halo=None, tblock=0):
+def _worker(rank, world, port, name, shape, steps, q, halo=None, tblock=0, ty="f64"):
     import torch
     import torch.distributed as dist
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
@@ -29,8 +29,9 @@ def _worker(rank, world, port, name, shape, steps, q, halo=None, tblock=0):
     try:
         import neptune_pde_solver_b200 as nb
         from neptune_pde_solver_b200.slab import Slab
-        gtext, n_extra = H.program(name, list(shape))
-        u, extra = H.inputs(shape, n_extra, "f64", seed=99)
+        gtext, n_extra = H.program(name, list(shape), ty)
+        u, extra = H.inputs(shape, n_extra, ty, seed=99)
+        dt = H.NPT[ty]
         g = nb.Module(gtext).apply_desc(0)
         s = Slab(g, world, rank, halo)
         ctx = nb.Context(rank)
@@ -40,13 +41,13 @@ def _worker(rank, world, port, name, shape, steps, q, halo=None, tblock=0):
         st = s.stencil(ctx)
         st.set("tblock", tblock)
         lb, ub = s.local.out_lb, s.local.out_ub
-        fa, fb = nb.Field(ctx, np.float64, lb, ub), nb.Field(ctx, np.float64, lb, ub)
+        fa, fb = nb.Field(ctx, dt, lb, ub), nb.Field(ctx, dt, lb, ub)
         loc = s.scatter(u)
         fa.upload(loc)
         fb.upload(loc)
         fx = []
         for e in extra:
-            f = nb.Field(ctx, np.float64, lb, ub)
+            f = nb.Field(ctx, dt, lb, ub)
             f.upload(s.scatter(e))
             fx.append(f)
         res = st.run_steps(fa, fb, fx, steps)
@@ -77,6 +78,16 @@ def _worker(rank, world, port, name, shape, steps, q, halo=None, tblock=0):
     ("heat_star", (48, 20, 256), 6, 2, 0),     # wide box: the z-marching kernel (tb2m) in slab mode
     ("heat_box_2d9", (96, 1040), 8, 2, 0),     # rank 2, two ghost rows: sweep_rows2 in slab mode
     ("jacobi_star", (64, 40, 72), 8, 2, 0),    # fused pairs with a pointwise right-hand side: f's ghost planes are exchanged once
+    ("varcoef_3d27", (32, 16, 32), 3, None, 0),   # BASELINE configs[3]'s body: 27 coefficient fields, NCCL halos
+    ("varcoef_3d27", (48, 16, 32), 4, 2, 0),      # ... computing ghost planes too (coefficient ghosts exchanged once)
+    ("heat_star", (64, 48, 64), 10, 4, 0),        # deep halos: four ghost planes, one exchange per TWO fused pairs
+    ("heat_star", (70, 48, 64), 9, 4, 0),         # ... uneven slabs (70 planes over the ranks) and an odd step count
+    ("heat_star", (96, 40, 264), 12, 8, 0),       # eight ghost planes: one exchange per four fused pairs, wide box (tb2p / tb2q interior)
+    ("jacobi_star", (64, 40, 72), 8, 4, 0),       # deep halos with a pointwise right-hand side
+    ("heat_star", (64, 48, 64), 7, 3, 1),         # single steps with three ghost planes: one exchange per three steps
+    ("heat_box_2d9", (96, 1040), 8, 4, 0),        # rank 2, four ghost rows
+    ("heat_star", (24, 24, 64), 6, 4, 0),         # slabs thinner than two halos on four ranks: unsplit sweep, serial exchange (agreed by all ranks)
+    ("varcoef_3d7", (48, 16, 32), 5, 2, 0),       # single-step kernel computing one ghost plane per launch
 ])
 def test_slab_nccl_equals_single_domain(name, shape, steps, halo, tblock):
     import torch
@@ -98,3 +109,27 @@ def test_slab_nccl_equals_single_domain(name, shape, steps, halo, tblock):
     assert ok is True
     if halo == 2 and tblock != 1 and name in ("heat_star", "jacobi_star", "heat_box_2d9") and steps % 2 == 0:
         assert used.startswith("tb2"), used   # the temporally blocked kernel really ran in slab mode
+
+
+@pytest.mark.parametrize("ty", ["f64", "f32"])
+def test_jacobi_1000_iterations_slabs_bit_exact(ty):
+    """BASELINE configs[4] at reduced size: 1000 Jacobi iterations with a right-hand side on 96^3 over the slabs of up
+    to four GPUs, four ghost planes (two fused pairs per exchange), every iteration's rounding reproduced: the result
+    equals the oracle's 1000-step loop bitwise."""
+    import torch
+    import torch.multiprocessing as mp
+    ngpu = torch.cuda.device_count()
+    if ngpu < 2:
+        pytest.skip("needs >= 2 GPUs")
+    world = min(ngpu, 4)
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_worker, args=(r, world, port, "jacobi_star", (96, 96, 96), 1000, q, 4, 0, ty)) for r in range(world)]
+    for p in procs:
+        p.start()
+    for p in procs:
+        p.join(600)
+        assert p.exitcode == 0
+    ok, used = q.get(timeout=5)
+    assert ok is True and used.startswith("tb2"), used

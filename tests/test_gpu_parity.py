@@ -390,7 +390,7 @@ def test_temporal_blocking_bit_exact(nb, ctx, name, shape, ty, steps):
         st = m.stencil(ctx, 0)
         ran = []
         for tbv in ["tb2:64x16", "tb2:64x16n7", "tb2:128x16", "tb2:64x32", "tb2m:128x14", "tb2m:64x16", "tb2m:128x14n8", "tb2m:64x24",
-                    "tb2g:128x14", "tb2g:64x24", "tb2p:128x14", "tb2p:64x24"]:
+                    "tb2g:128x14", "tb2g:64x24", "tb2p:128x14", "tb2p:64x24", "tb2q:128x14"]:
             try:
                 st.set("variant", tbv)
             except nb.NeptuneError:
@@ -785,7 +785,7 @@ def test_matrix_free_operator_on_caller_owned_device_vectors(nb, ctx):
 
 
 @pytest.mark.parametrize("name,shape,variants", [
-    ("heat_star", (96, 112, 256), ["tb2:128x16", "tb2m:128x14", "tb2g:128x14", "tb2m:64x24", "tb2p:128x14", "tb2p:64x24"]),
+    ("heat_star", (96, 112, 256), ["tb2:128x16", "tb2m:128x14", "tb2g:128x14", "tb2m:64x24", "tb2p:128x14", "tb2p:64x24", "tb2q:128x14"]),
     ("heat_box_2d9", (1536, 2032), ["tb2r:256x3", "tb2r:512x3"]),
     ("jacobi_star", (96, 96, 192), ["tb2m:64x24", "tb2m:128x14"]),
 ])
