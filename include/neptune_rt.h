@@ -44,7 +44,7 @@ extern "C" {
 #define NEPTUNE_RT_EINVAL (-1)      /* bad argument / malformed descriptor              */
 #define NEPTUNE_RT_ENODEV (-2)      /* no CUDA device / driver (there is no CPU path)   */
 #define NEPTUNE_RT_ECUDA (-3)       /* a CUDA call failed                               */
-#define NEPTUNE_RT_EUNSUPPORTED (-4)/* body is outside the compiled stencil catalogue   */
+#define NEPTUNE_RT_EUNSUPPORTED (-4)/* outside the recognised set / cannot be compiled     */
 #define NEPTUNE_RT_ENCCL (-5)       /* NCCL missing or a collective failed              */
 #define NEPTUNE_RT_ENOMEM (-6)
 
@@ -151,8 +151,15 @@ int neptune_rt_field_reduce_sum(neptune_rt_field *field, const int64_t *lb, cons
 /* 64-bit structure key of a body (constants' values, bounds and extents excluded): two applies
  * with the same key run the same compiled kernel. Pure host code. */
 uint64_t neptune_rt_body_key(const neptune_rt_stencil_desc *desc);
-/* 1 when the library holds compiled sm_100a kernels for this body key. Pure host code. */
+/* 1 when the library holds compiled sm_100a kernels for this body key (prebuilt catalogue, or a body already
+ * compiled at run time in this process). Pure host code. */
 int neptune_rt_body_compiled(uint64_t key);
+/* Bodies outside the prebuilt catalogue are compiled on first use by neptune_rt_stencil_create: NVRTC builds the same
+ * hand-written sweep kernels for the body's generated point functor (sm_100a cubin, cached on disk under
+ * $NEPTUNE_B200_JIT_CACHE or ~/.cache/neptune_b200_jit), so every body the recogniser accepts runs — the reference
+ * lowers any body too (lib/Passes/DataflowLowering.cpp:413-423). This entry does only the compile step (no GPU
+ * needed): it fills the cache ahead of time and reports the compile time. */
+int neptune_rt_body_jit_compile(const neptune_rt_stencil_desc *desc, double *seconds, char *err, size_t err_len);
 int neptune_rt_stencil_create(neptune_rt_ctx *ctx, const neptune_rt_stencil_desc *desc,
                               neptune_rt_stencil **stencil);
 int neptune_rt_stencil_destroy(neptune_rt_stencil *stencil);

@@ -35,7 +35,7 @@ NVCC_FLAGS = ARCH + ["-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC", "-
 CXX_FLAGS = ["-O2", "-std=c++17", "-fPIC", "-Wall", "-I", CSRC, "-I", INCLUDE]
 
 FRONTEND = ["frontend/parser.cpp", "frontend/recognizer.cpp", "frontend/codegen.cpp", "frontend/fusion.cpp"]
-HOST_SRCS = FRONTEND + ["frontend/module.cpp", "runtime/registry.cpp"]
+HOST_SRCS = FRONTEND + ["frontend/module.cpp", "runtime/registry.cpp", "runtime/jit.cpp"]
 CUDA_SRCS = ["runtime/runtime.cu"]
 KERNEL_HEADERS = sorted(glob.glob(os.path.join(CSRC, "kernels", "*"))) + sorted(glob.glob(os.path.join(CSRC, "frontend", "*.h"))) \
     + sorted(glob.glob(os.path.join(INCLUDE, "*.h")))

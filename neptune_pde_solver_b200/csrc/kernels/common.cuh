@@ -10,9 +10,26 @@
 // (lib/Passes/DataflowLowering.cpp:413-423) — so with FMA = false the result is bit-identical
 // to the CPU lowering.
 #pragma once
+#ifdef __CUDACC_RTC__
+// NVRTC (runtime/jit.cpp compiles bodies outside the prebuilt catalogue): no host headers
+typedef unsigned char uint8_t;
+typedef unsigned int uint32_t;
+typedef int int32_t;
+typedef unsigned long long uint64_t;
+typedef long long int64_t;
+typedef unsigned long long uintptr_t;
+namespace std {
+template <class T, T V> struct integral_constant {
+  static constexpr T value = V;
+  typedef T value_type;
+  constexpr operator T() const noexcept { return V; }
+};
+}  // namespace std
+#else
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <type_traits>
+#endif
 
 namespace neptune {
 

@@ -4,15 +4,7 @@
 #include <algorithm>
 
 #include "registry.h"
-#include "sweep_direct.cuh"
-#include "sweep_tma.cuh"
-#include "sweep_tb2.cuh"
-#include "sweep_tb2m.cuh"
-#include "sweep_tb2g.cuh"
-#include "sweep_tb2p.cuh"
-#include "sweep_tb2q.cuh"
-#include "sweep_rows.cuh"
-#include "sweep_rows2.cuh"
+#include "tiles.cuh"
 
 namespace neptune {
 
@@ -42,26 +34,6 @@ template <class F, bool FMA> int launch_direct(const SweepArgs &a) {
   if (grid.y > 65535u || grid.z > 65535u) return (int)cudaErrorInvalidConfiguration;
   sweep_direct<F, FMA><<<grid, dim3(DIRECT_BX, DIRECT_BY, 1), 0, a.stream>>>(p);
   return (int)cudaGetLastError();
-}
-
-// planes per work item: keep every CTA slot of the persistent grid busy for the same number of
-// rounds (items / (rounds * slots)) while paying as little z-halo re-read per chunk as possible
-inline int choose_zchunk(int planes, int ncols, int grid_slots, int rz) {
-  if (rz == 0 || planes <= 1) return std::max(planes, 1);
-  const int cand[] = {16, 24, 32, 48, 64, 96, 128, 192, 256, planes};
-  double best = -1;
-  int best_zc = planes;
-  for (int zc : cand) {
-    if (zc > planes) zc = planes;
-    const long long chunks = (planes + zc - 1) / zc;
-    const long long items = chunks * ncols;
-    const long long rounds = (items + grid_slots - 1) / grid_slots;
-    const double balance = (double)items / (double)(rounds * grid_slots);
-    const double halo = (double)zc / (double)(zc + 2 * rz);
-    const double score = balance * halo;
-    if (score > best + 1e-9) { best = score; best_zc = zc; }
-  }
-  return best_zc;
 }
 
 // two boundary ranges [wlo, gap_lo) and [gap_hi, whi) of the marching dimension `dim` as chunks 0 and 1 of one launch
@@ -119,7 +91,7 @@ template <class F, class C, int MARCH> struct Tb2GeomOf { typedef Tb2Geom<F, C> 
 template <class F, class C> struct Tb2GeomOf<F, C, 1> { typedef Tb2mGeom<F, C> type; };
 template <class F, class C> struct Tb2GeomOf<F, C, 2> { typedef Tb2gGeom<F, C> type; };
 template <class F, class C> struct Tb2GeomOf<F, C, 3> { typedef Tb2pGeom<F, C> type; };
-template <class F, class C> struct Tb2GeomOf<F, C, 4> { typedef Tb2pGeom<F, C> type; };
+template <class F, class C> struct Tb2GeomOf<F, C, 4> { typedef Tb2qGeom<F, C> type; };
 
 template <class F, class C, bool FMA, int MARCH = 0> int launch_tb2(const SweepArgs &a) {
   typedef typename Tb2GeomOf<F, C, MARCH>::type G;
@@ -302,42 +274,6 @@ template <class F, class C, bool FMA> Variant tma_variant(const char *name) {
   v.launch = &launch_tma<F, C, FMA>;
   return v;
 }
-
-// tile menus (elements).  3-D bodies march in z; bodies without z taps (2-D) take bigger tiles.
-typedef TileCfg<64, 16, 2, 8, 2> Tile3A;    // r01 sweep on C3: 348 Gupd/s (0.864 of the measured copy peak)
-typedef TileCfg<128, 8, 2, 8, 2> Tile3B;
-typedef TileCfg<128, 16, 4, 5, 2> Tile3C;
-typedef Tb2Cfg<64, 16, 2, 5, 2> Tb2A;       // two time steps per launch (sweep_tb2.cuh)
-typedef Tb2Cfg<64, 16, 2, 7, 1> Tb2B;
-typedef Tb2Cfg<128, 16, 2, 5, 1> Tb2C;
-typedef Tb2Cfg<64, 32, 4, 5, 1> Tb2D;
-// z-marching form (sweep_tb2m.cuh).  Registers are granted per warp in units of 512, so a CTA of 704
-// threads (128x16 tile) gets 80 per thread and spills; 128x14 is 640 threads -> 96 registers.
-typedef Tb2Cfg<128, 14, 2, 6, 1> Tb2mA;
-typedef Tb2Cfg<64, 16, 2, 6, 2> Tb2mB;
-typedef Tb2Cfg<128, 14, 2, 8, 1> Tb2mC;
-// 512 threads = 4 warps per SM sub-partition -> up to 128 registers (5 warps per sub-partition: 96)
-typedef Tb2Cfg<64, 24, 2, 8, 1> Tb2mD;
-typedef Tb2Cfg<128, 10, 2, 6, 1> Tb2mE;
-typedef Tb2Cfg<64, 24, 2, 5, 1> Tb2mG;
-typedef Tb2pCfg<128, 14, 2, 4, 1, 3> Tb2pA;   // seven level-1 planes leave room for four level-0 slots
-typedef Tb2pCfg<64, 24, 2, 6, 1, 3> Tb2pB;
-
-typedef Tb2Cfg<128, 14, 2, 4, 1> Tb2mF;   // two staged tiles per slot: four slots fit beside the level-1 planes
-typedef TileCfg<64, 8, 1, 6, 1> Tile3W;   // many-input bodies (one coefficient field per tap)
-typedef TileCfg<64, 7, 1, 6, 2> Tile3W2;  // 256 threads, two CTAs per SM at 128 registers
-typedef TileCfg<64, 14, 1, 5, 1> Tile3W3; // 480 threads, one CTA per SM at 128 registers
-// strip of TX columns, RB rows per stage (a multiple of the 3-row window, so the unrolled stage loop needs
-// no register moves), ring of NS stages, CTAs per SM
-typedef RowCfg<512, 3, 5, 3> Rows512;
-typedef RowCfg<256, 6, 4, 4> Rows256;
-typedef RowCfg<1024, 3, 4, 1> Rows1024;
-typedef Rows2Cfg<256, 3, 5, 2> Rows2A;     // 256 consumer threads (strip of 508 f64 columns), 3 rows per stage, two CTAs per SM
-typedef Rows2Cfg<256, 6, 4, 1> Rows2B;
-typedef Rows2Cfg<512, 3, 4, 1> Rows2C;
-typedef TileCfg<128, 32, 8, 3, 2> Tile2A;
-typedef TileCfg<128, 16, 4, 4, 2> Tile2B;
-typedef TileCfg<64, 64, 8, 3, 2> Tile2C;
 
 template <class F> struct BodyRegistrar {
   BodyRegistrar() {

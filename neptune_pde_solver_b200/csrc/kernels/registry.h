@@ -6,6 +6,9 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include <algorithm>
+#include <deque>
+#include <functional>
 #include <string>
 #include <vector>
 
@@ -46,7 +49,7 @@ struct Variant {
   int steps = 1;                // time steps one launch advances (2: temporally blocked)
   bool needs_tmap = true;       // TMA / TB2 kinds: the launch takes a tensor map of the staged input (row kernels use bulk copies)
   int gap_dim = -1;             // canonical dimension in which the launch honours SweepArgs::gap_lo/gap_hi (-1: it cannot)
-  int (*launch)(const SweepArgs &) = nullptr;   // returns a cudaError_t
+  std::function<int(const SweepArgs &)> launch;   // returns a cudaError_t (generated units: a launcher template; JIT bodies: a closure over the loaded kernel)
 };
 
 struct BodyEntry {
@@ -55,8 +58,34 @@ struct BodyEntry {
   std::vector<Variant> variants;
 };
 
+// the table keeps addresses stable (stencils hold BodyEntry pointers while the JIT registers more bodies)
 void register_body(BodyEntry &&e);
 const BodyEntry *find_body(uint64_t key);
-const std::vector<BodyEntry> &all_bodies();
+const std::deque<BodyEntry> &all_bodies();
+
+// planes per work item: keep every CTA slot of the persistent grid busy for the same number of
+// rounds (items / (rounds * slots)) while paying as little z-halo re-read per chunk as possible
+inline int choose_zchunk(int planes, int ncols, int grid_slots, int rz) {
+  if (rz == 0 || planes <= 1) return std::max(planes, 1);
+  const int cand[] = {16, 24, 32, 48, 64, 96, 128, 192, 256, planes};
+  double best = -1;
+  int best_zc = planes;
+  for (int zc : cand) {
+    if (zc > planes) zc = planes;
+    const long long chunks = (planes + zc - 1) / zc;
+    const long long items = chunks * ncols;
+    const long long rounds = (items + grid_slots - 1) / grid_slots;
+    const double balance = (double)items / (double)(rounds * grid_slots);
+    const double halo = (double)zc / (double)(zc + 2 * rz);
+    const double score = balance * halo;
+    if (score > best + 1e-9) { best = score; best_zc = zc; }
+  }
+  return best_zc;
+}
+
+// Bodies outside the prebuilt catalogue (runtime/jit.cpp): NVRTC-compile kernels/tiles.cuh + the generated functor for
+// `desc`, load the cubin on `device` and register the variants; the cubin is cached on disk by key + header digest.
+// Returns 0 or a NEPTUNE_RT_E* code with `err` filled. compile_only: stop after the cubin is built / found (no GPU needed).
+int jit_body(const neptune_rt_stencil_desc &desc, int device, bool compile_only, std::string &err, double *seconds);
 
 }  // namespace neptune

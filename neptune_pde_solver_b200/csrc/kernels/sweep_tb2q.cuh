@@ -76,10 +76,46 @@ __device__ __forceinline__ void load_halo_s(T (&c)[VY + 2][VX + 2], uint32_t blk
   });
 }
 
+// Row pitches.  A warp covers 32 consecutive thread blocks of the NBX-wide thread grid, so most warps straddle two
+// thread rows (NBX = 66 for the 128-wide f64 tile); the 16-byte accesses of a quarter-warp then fall into two row
+// segments VY shared-memory rows apart, and with the natural pitches those overlap in banks (r02 ncu of the first
+// tb2q: 15.0 M of 95.9 M shared wavefronts per launch were bank-conflict replays, the shared pipe at 67 % being the
+// busiest unit).  Padding the pitch so that VY * pitch = NBX * 16 (mod 128) makes the second row continue the bank
+// sequence where the first one stopped: a straddling quarter-warp touches every bank once, as a contiguous one does.
+constexpr int tb2q_pitch(int min_elems, int vx, int vy, int nbx, int s) {
+  int p = min_elems;
+  while (((vy * p * s - nbx * 16) % 128 + 128) % 128 != 0) p += vx;
+  return p;
+}
+
+template <class F, class C> struct Tb2qGeom {
+  typedef typename F::T T;
+  typedef Tb2mGeom<F, C> B;
+  static constexpr int S = sizeof(T);
+  static constexpr int VX = B::VX, VY = B::VY, NBX = B::NBX, NBY = B::NBY;
+  static constexpr int ACTIVE = B::ACTIVE, CONSUMERS = B::CONSUMERS, THREADS = B::THREADS, NS = B::NS;
+  static constexpr int GS = C::GS, NL1 = 2 * GS + 1;
+  static constexpr int P0 = tb2q_pitch(C::TX + 4 * VX, VX, VY, NBX, S);   // level-0 stage row pitch = TMA box width
+  static constexpr int BOX_Y = C::TY + 4;
+  static constexpr int STAGE_TX_BYTES = P0 * BOX_Y * S;
+  static constexpr int STAGE_BYTES = (STAGE_TX_BYTES + 127) / 128 * 128;
+  static constexpr int SLOT_BYTES = STAGE_BYTES;
+  static constexpr int GUARD_BYTES = (P0 * S * (VY > 2 ? VY - 1 : 1) + 127) / 128 * 128;
+  static constexpr int P1 = tb2q_pitch(NBX * VX, VX, VY, NBX, S), H1 = NBY * VY;   // level-1 plane
+  static constexpr int L1_BYTES = (P1 * H1 * S + 127) / 128 * 128;
+  static constexpr int L1_GUARD = (P1 * S + 127) / 128 * 128;
+  static constexpr int SMEM_BYTES = GUARD_BYTES + NS * SLOT_BYTES + GUARD_BYTES + L1_GUARD + NL1 * L1_BYTES + L1_GUARD + 2 * NS * 8 + 128;
+  static_assert(GS == 3, "three planes per barrier group");
+  static_assert(F::NIN == 1, "single-input bodies");
+  static_assert(P0 <= 256 && BOX_Y <= 256, "TMA box dimensions are limited to 256 elements");
+  static_assert((P0 * S) % 16 == 0, "TMA box rows are multiples of 16 bytes");
+  static_assert(SMEM_BYTES <= 227 * 1024, "rings do not fit in shared memory");
+};
+
 template <class F, class C, bool FMA>
-__global__ void __launch_bounds__((Tb2pGeom<F, C>::THREADS), C::MINB)
+__global__ void __launch_bounds__((Tb2qGeom<F, C>::THREADS), C::MINB)
 sweep_tb2q(const __grid_constant__ KParams<F> p, const __grid_constant__ CUtensorMap tmap) {
-  typedef Tb2pGeom<F, C> G;
+  typedef Tb2qGeom<F, C> G;
   typedef typename F::T T;
   constexpr int VX = G::VX, VY = G::VY, NS = G::NS;
   constexpr int NCW = G::CONSUMERS / 32;
@@ -123,8 +159,15 @@ sweep_tb2q(const __grid_constant__ KParams<F> p, const __grid_constant__ CUtenso
         int zb, ze, y0, x0;
         geom(item, zb, ze, y0, x0);
         const int nslots = ze - zb + 4;
+        // the ring holds NS = 4 planes, about two plane-steps of look-ahead (r02 ncu: the consumers still waited on the
+        // full barriers, long_scoreboard 1.47 per issue).  Shared memory has no room for more stages, L2 has: the
+        // producer asks the TMA unit to PREFETCH plane j + PF into L2 when it loads plane j, so the load proper is an
+        // L2 hit.
+        constexpr int PF = C::NS + 4;
+        for (int j = 0; j < min(PF, nslots); ++j) tma_prefetch_3d(&tmap, x0 - 2 * VX, y0 - 2, zb - 2 + j);
         for (int j = 0; j < nslots; ++j, ++n) {
           const unsigned s = n % NS;
+          if (j + PF < nslots) tma_prefetch_3d(&tmap, x0 - 2 * VX, y0 - 2, zb - 2 + j + PF);
           mbar_wait(empty0 + 8 * s, ((n / NS) & 1) ^ 1);
           mbar_expect_tx(full0 + 8 * s, G::STAGE_TX_BYTES);
           tma_load_3d(stage0 + s * G::SLOT_BYTES, &tmap, x0 - 2 * VX, y0 - 2, zb - 2 + j, full0 + 8 * s);
@@ -143,6 +186,7 @@ sweep_tb2q(const __grid_constant__ KParams<F> p, const __grid_constant__ CUtenso
   const bool inner = active && bx >= 1 && bx <= G::NBX - 2 && by >= 1 && by <= G::NBY - 2;
   const bool lane0 = (tid & 31) == 0;
   const bool swap = ((tid >> 3) & 1) != 0;
+  const bool ring_warp = __all_sync(0xffffffffu, !inner);   // warp-uniform
   // this thread's block inside level-0 slot 0 / level-1 plane 0, as shared-window byte addresses
   const uint32_t t0 = stage0 + (uint32_t)(((by * VY - VY + 2) * G::P0 + VX + bx * VX) * S);
   const uint32_t t1 = smem_u32(l1) + (uint32_t)(((by * VY) * G::P1 + bx * VX) * S);
@@ -198,9 +242,9 @@ sweep_tb2q(const __grid_constant__ KParams<F> p, const __grid_constant__ CUtenso
     for (int j0 = 0; j0 < nslots + GS; j0 += GS) {
       if (j0 == g_lo && n_lean > 0) {
         // ---- lean groups: three steady steps, every plane inside the z bounds ------------------------
-        for (int g = n_lean; g > 0; --g)
-        static_for<GS>([&](auto rc) {
+        auto lean_step = [&](auto rc, auto with_b) {
           constexpr int R = decltype(rc)::value;
+          constexpr bool WITH_B = decltype(with_b)::value != 0;
           constexpr int A0 = R % 3, A1 = (R + 1) % 3, A2 = (R + 2) % 3;
           T wa[VY + 2][VX + 2], wb[VY + 2][VX + 2];
           mbar_wait(fullb + 8 * s, ph);
@@ -213,14 +257,19 @@ sweep_tb2q(const __grid_constant__ KParams<F> p, const __grid_constant__ CUtenso
           prv = cur;
           if (++s == NS) { s = 0; ph ^= 1; }
           // level-1 reads of phase B' (planes produced before the last barrier)
-          const uint32_t pnew = t1 + slot(c1, GS + 1) * (uint32_t)G::L1_BYTES;   // plane k-LAG+1
-          const uint32_t pctr = t1 + slot(c1, GS) * (uint32_t)G::L1_BYTES;       // plane k-LAG
-          static_for<VY>([&](auto r) { lds16<decltype(r)::value * PB1>(b[A2][decltype(r)::value], pnew); });
-          load_halo_s<T, VX, VY, PB1, CORNERS>(wb, pctr, pctr + o_lr, pctr + o_rl, swp != 0u);
+          if constexpr (WITH_B) {
+            const uint32_t pnew = t1 + slot(c1, GS + 1) * (uint32_t)G::L1_BYTES;   // plane k-LAG+1
+            const uint32_t pctr = t1 + slot(c1, GS) * (uint32_t)G::L1_BYTES;       // plane k-LAG
+            static_for<VY>([&](auto r) { lds16<decltype(r)::value * PB1>(b[A2][decltype(r)::value], pnew); });
+            load_halo_s<T, VX, VY, PB1, CORNERS>(wb, pctr, pctr + o_lr, pctr + o_rl, swp != 0u);
+          }
 #pragma unroll
           for (int iy = 0; iy < VY; ++iy)
 #pragma unroll
-            for (int ix = 0; ix < VX; ++ix) { wa[1 + iy][1 + ix] = a[A1][iy][ix]; wb[1 + iy][1 + ix] = b[A1][iy][ix]; }
+            for (int ix = 0; ix < VX; ++ix) {
+              wa[1 + iy][1 + ix] = a[A1][iy][ix];
+              if constexpr (WITH_B) wb[1 + iy][1 + ix] = b[A1][iy][ix];
+            }
           // both levels, unconditionally, one basic block
           T ra[VY][VX], res[VY][VX];
           static_for<VY>([&](auto iyc) {
@@ -229,8 +278,10 @@ sweep_tb2q(const __grid_constant__ KParams<F> p, const __grid_constant__ CUtenso
               constexpr int IX = decltype(ixc)::value;
               MarchAcc<F, VY, VX, IY, IX> acca{a[A0], wa, a[A2], nopw};
               ra[IY][IX] = F::template eval<FMA>(acca, p.c);
-              MarchAcc<F, VY, VX, IY, IX> accb{b[A0], wb, b[A2], nopw};
-              res[IY][IX] = F::template eval<FMA>(accb, p.c);
+              if constexpr (WITH_B) {
+                MarchAcc<F, VY, VX, IY, IX> accb{b[A0], wb, b[A2], nopw};
+                res[IY][IX] = F::template eval<FMA>(accb, p.c);
+              }
             });
           });
           if (nb != 0u) {   // threads on the y/x edge of the apply bounds only: copy-through of both levels
@@ -239,24 +290,40 @@ sweep_tb2q(const __grid_constant__ KParams<F> p, const __grid_constant__ CUtenso
             for (int iy = 0; iy < VY; ++iy)
 #pragma unroll
               for (int ix = 0; ix < VX; ++ix)
-                if ((nb >> (iy * VX + ix)) & 1u) { ra[iy][ix] = a[A1][iy][ix]; res[iy][ix] = b[A1][iy][ix]; }
+                if ((nb >> (iy * VX + ix)) & 1u) {
+                  ra[iy][ix] = a[A1][iy][ix];
+                  if constexpr (WITH_B) res[iy][ix] = b[A1][iy][ix];
+                }
           }
           const uint32_t l1p = t1 + c1 * (uint32_t)G::L1_BYTES;
           static_for<VY>([&](auto r) { sts16<decltype(r)::value * PB1>(l1p, ra[decltype(r)::value]); });
-          if (wmask == ALL) {
+          if constexpr (WITH_B) {
+            if (wmask == ALL) {
 #pragma unroll
-            for (int iy = 0; iy < VY; ++iy) stg_vec<T, VX, false>(dst + iy * p.out_sy, res[iy]);
-          } else if (wmask != 0u) {   // tiles cut by the edge of the written box
+              for (int iy = 0; iy < VY; ++iy) stg_vec<T, VX, false>(dst + iy * p.out_sy, res[iy]);
+            } else if (wmask != 0u) {   // tiles cut by the edge of the written box
 #pragma unroll
-            for (int iy = 0; iy < VY; ++iy)
+              for (int iy = 0; iy < VY; ++iy)
 #pragma unroll
-              for (int ix = 0; ix < VX; ++ix)
-                if ((wmask >> (iy * VX + ix)) & 1u) dst[iy * p.out_sy + ix] = res[iy][ix];
+                for (int ix = 0; ix < VX; ++ix)
+                  if ((wmask >> (iy * VX + ix)) & 1u) dst[iy * p.out_sy + ix] = res[iy][ix];
+            }
+            dst += p.out_sz;
           }
-          dst += p.out_sz;
           c1 = slot(c1, 1u);
           if constexpr (R == GS - 1) asm volatile("bar.sync 1, %0;" ::"n"(G::CONSUMERS) : "memory");
-        });
+        };
+        // warps made of ring threads only (the first and last thread rows: four of the twenty consumer warps of the
+        // 128x14 tile) have no level-2 points: their own copy of the loop does phase A alone — no level-1 reads
+        // (24 shared wavefronts per warp and step), no second evaluation
+        if (ring_warp) {
+          for (int g = n_lean; g > 0; --g)
+            static_for<GS>([&](auto rc) { lean_step(rc, std::integral_constant<int, 0>{}); });
+        } else {
+          for (int g = n_lean; g > 0; --g)
+            static_for<GS>([&](auto rc) { lean_step(rc, std::integral_constant<int, 1>{}); });
+          // (dst advanced with the steps)
+        }
         j0 += GS * n_lean;
       }
       // ---- general group: pipeline fill / drain and planes on the z edge of the bounds (fully masked) ----

@@ -24,7 +24,12 @@
 // staged centre value, which IS input 0 — the host only selects this kernel when input 0 is the
 // staged input).
 #pragma once
+#ifdef __CUDACC_RTC__
+struct alignas(64) CUtensorMap_st { unsigned long long opaque[16]; };   // <cuda.h>'s definition; NVRTC has no host headers
+typedef CUtensorMap_st CUtensorMap;
+#else
 #include <cuda.h>
+#endif
 
 #include "common.cuh"
 
@@ -101,6 +106,10 @@ __device__ __forceinline__ void tma_load_3d(uint32_t dst, const CUtensorMap *map
       "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];"
       ::"r"(dst), "l"((uint64_t)map), "r"(x), "r"(y), "r"(z), "r"(bar)
       : "memory");
+}
+
+__device__ __forceinline__ void tma_prefetch_3d(const CUtensorMap *map, int x, int y, int z) {
+  asm volatile("cp.async.bulk.prefetch.tensor.3d.L2.global.tile [%0, {%1, %2, %3}];" ::"l"((uint64_t)map), "r"(x), "r"(y), "r"(z) : "memory");
 }
 
 template <class T> struct Vec16;

@@ -6,8 +6,8 @@
 
 namespace neptune {
 
-static std::vector<BodyEntry> &table() {
-  static std::vector<BodyEntry> t;
+static std::deque<BodyEntry> &table() {
+  static std::deque<BodyEntry> t;
   return t;
 }
 
@@ -23,6 +23,6 @@ const BodyEntry *find_body(uint64_t key) {
   return nullptr;
 }
 
-const std::vector<BodyEntry> &all_bodies() { return table(); }
+const std::deque<BodyEntry> &all_bodies() { return table(); }
 
 }  // namespace neptune

@@ -595,6 +595,20 @@ extern "C" int neptune_rt_field_reduce_sum(neptune_rt_field *f, const int64_t *l
 // ---------------------------------------------------------------------------------------------
 extern "C" uint64_t neptune_rt_body_key(const neptune_rt_stencil_desc *d) { return d ? neptune::body_key(*d) : 0; }
 extern "C" int neptune_rt_body_compiled(uint64_t key) { return neptune::find_body(key) ? 1 : 0; }
+extern "C" int neptune_rt_body_jit_compile(const neptune_rt_stencil_desc *d, double *seconds, char *err, size_t err_len) {
+  if (!d) return NEPTUNE_RT_EINVAL;
+  std::string e;
+  int rc;
+  try {
+    neptune::validate_desc(*d);
+    rc = neptune::jit_body(*d, 0, true, e, seconds);
+  } catch (const neptune::Diagnostic &dg) {
+    e = dg.what();
+    rc = dg.unsupported ? NEPTUNE_RT_EUNSUPPORTED : NEPTUNE_RT_EINVAL;
+  }
+  if (err && err_len) std::snprintf(err, err_len, "%s", e.c_str());
+  return rc;
+}
 
 extern "C" int neptune_rt_stencil_create(neptune_rt_ctx *c, const neptune_rt_stencil_desc *d, neptune_rt_stencil **out) {
   if (!c || !d || !out) return set_error(c, NEPTUNE_RT_EINVAL, "neptune_rt_stencil_create: NULL argument");
@@ -606,11 +620,21 @@ extern "C" int neptune_rt_stencil_create(neptune_rt_ctx *c, const neptune_rt_ste
   }
   const uint64_t key = neptune::body_key(*d);
   const BodyEntry *be = neptune::find_body(key);
-  if (!be)
-    return set_error(c, NEPTUNE_RT_EUNSUPPORTED,
-                     "apply body with structure key 0x%016llx is not in the compiled sm_100a kernel catalogue "
-                     "(%zu bodies); add its .mlir to the catalogue and rebuild — there is no CPU fallback",
-                     (unsigned long long)key, neptune::all_bodies().size());
+  if (!be) {
+    // not in the prebuilt catalogue: the same hand-written kernels, compiled for this body now (runtime/jit.cpp).
+    // The reference lowers any body (DataflowLowering.cpp:413-423); NEPTUNE_RT_JIT=0 restores the closed catalogue.
+    const char *off = std::getenv("NEPTUNE_RT_JIT");
+    std::string err;
+    int rc = NEPTUNE_RT_EUNSUPPORTED;
+    if (off && off[0] == '0') err = "run-time compilation is switched off (NEPTUNE_RT_JIT=0)";
+    else rc = neptune::jit_body(*d, c->device, false, err, nullptr);
+    be = rc == NEPTUNE_RT_OK ? neptune::find_body(key) : nullptr;
+    if (!be)
+      return set_error(c, rc ? rc : NEPTUNE_RT_EUNSUPPORTED,
+                       "apply body with structure key 0x%016llx is not in the prebuilt sm_100a kernel catalogue (%zu bodies) and could "
+                       "not be compiled at run time: %s — there is no CPU fallback",
+                       (unsigned long long)key, neptune::all_bodies().size(), err.c_str());
+  }
   neptune_rt_stencil *s = new neptune_rt_stencil();
   s->ctx = c;
   s->desc = StencilDesc::from_c(*d);
@@ -842,8 +866,10 @@ int do_apply(neptune_rt_stencil *s, int n_in, neptune_rt_field *const *in, neptu
       // one input, wide box (r01, 512^3 f64): tb2p:128x14 466, tb2m:128x14 427, tb2g:128x14 415, tb2:128x16 409 Gupd/s.
       // The pipelined form pays seven planes of fill and drain per item instead of four: thin launches (the
       // boundary planes of a slab) keep tb2m.
+      // r02: tb2q:128x14 (tb2p's data movement with a lean steady state, conflict-free ring pitches) 541+ Gupd/s
       const bool deep = (p1 - p0) - (g1 - g0) >= 24 && !gap;
-      const char *prefer[] = {n_in > 1 ? two_in : wide ? (deep ? "tb2p:128x14" : "tb2m:128x14") : "tb2:64x16",
+      const char *prefer[] = {n_in > 1 ? two_in : wide ? (deep ? "tb2q:128x14" : "tb2m:128x14") : "tb2:64x16",
+                              wide && deep ? "tb2p:128x14" : wide ? "tb2m:128x14" : "tb2:64x16",
                               wide ? "tb2m:128x14" : "tb2:64x16"};
       for (const char *name : prefer) {
         for (auto &v : s->body->variants)

@@ -90,6 +90,7 @@ def lib() -> C.CDLL:
         "neptune_rt_field_reduce_sum": (i32, [vp, i64p, i64p, i32, C.POINTER(C.c_double)]),
         "neptune_rt_body_key": (C.c_uint64, [C.POINTER(StencilDescC)]),
         "neptune_rt_body_compiled": (i32, [C.c_uint64]),
+        "neptune_rt_body_jit_compile": (i32, [C.POINTER(StencilDescC), C.POINTER(C.c_double), C.c_char_p, C.c_size_t]),
         "neptune_rt_stencil_create": (i32, [vp, C.POINTER(StencilDescC), C.POINTER(vp)]),
         "neptune_rt_stencil_destroy": (i32, [vp]),
         "neptune_rt_stencil_set": (i32, [vp, C.c_char_p, C.c_char_p]),
@@ -200,6 +201,17 @@ class StencilDesc:
 
 def body_compiled(key: int) -> bool:
     return bool(lib().neptune_rt_body_compiled(C.c_uint64(key)))
+
+
+def body_jit_compile(desc: "StencilDesc") -> float:
+    """NVRTC-compile the sweep kernels for a body outside the prebuilt catalogue (fills the on-disk cache; needs no
+    GPU). Returns the seconds it took."""
+    sec = C.c_double()
+    err = C.create_string_buffer(4096)
+    rc = lib().neptune_rt_body_jit_compile(C.byref(desc.c()), C.byref(sec), err, len(err))
+    if rc:
+        raise NeptuneError(rc, err.value.decode())
+    return sec.value
 
 
 def slab_partition(n0: int, nranks: int, rank: int):

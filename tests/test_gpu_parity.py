@@ -318,13 +318,27 @@ def test_known_answers_on_device(nb, ctx):
 
 
 def test_errors_are_loud(nb, ctx):
-    # a body that is not in the compiled catalogue: EUNSUPPORTED, never a CPU fallback
+    import os
+    # a legal linear body that is NOT in the prebuilt catalogue (radius-2 taps): the reference lowers any body
+    # (DataflowLowering.cpp:413-423); here it is compiled at run time with NVRTC and runs, bit-exact
     text = H.mb.weighted_const([16, 16], [(0, 0), (0, 2), (2, 0)], [0.5, 0.25, 0.25])
-    m = nb.Module(text)     # recognised (it is a legal linear body) ...
-    with pytest.raises(nb.NeptuneError) as e:
-        m.run(ctx, "@entry", [np.zeros((16, 16)), np.zeros((16, 16))])
-    assert e.value.code == nb.runtime.EUNSUPPORTED and "catalogue" in str(e.value)
+    m = nb.Module(text)
+    u, _ = H.inputs((16, 16), 0, "f64", seed=3)
+    out = np.full_like(u, np.nan)
+    m.run(ctx, "@entry", [out, u])
+    assert H.bits_equal(out, H.oracle_entry(text, u, []))
     m.destroy()
+    # with run-time compilation switched off the catalogue is closed: EUNSUPPORTED, never a CPU fallback
+    os.environ["NEPTUNE_RT_JIT"] = "0"
+    try:
+        text = H.mb.weighted_const([16, 16], [(0, 0), (0, -2), (-2, 0)], [0.5, 0.25, 0.25])
+        m = nb.Module(text)     # recognised (it is a legal linear body) ...
+        with pytest.raises(nb.NeptuneError) as e:
+            m.run(ctx, "@entry", [np.zeros((16, 16)), np.zeros((16, 16))])
+        assert e.value.code == nb.runtime.EUNSUPPORTED and "catalogue" in str(e.value) and "no CPU fallback" in str(e.value)
+        m.destroy()
+    finally:
+        del os.environ["NEPTUNE_RT_JIT"]
     # result aliasing an input
     text, _ = H.program("heat_star", [8, 8, 8])
     m = nb.Module(text)
@@ -365,7 +379,16 @@ def test_launch_accounting(nb, ctx):
     n0 = ctx.launch_count()
     a, b = u.copy(), np.zeros_like(u)
     m.run_steps(ctx, "@entry", [b, a], 7)
-    assert ctx.launch_count() - n0 == 7      # one kernel per sweep: no copy-through or store kernels
+    # the entry's time loop is neptune_rt_run_steps: three fused pairs + one single sweep, and no copy-through
+    # or store kernels (one kernel per launch group)
+    assert ctx.launch_count() - n0 == 4
+    assert H.bits_equal([b, a][0], H.oracle_steps(text, u, [], 7))
+    m.stencil(ctx, 0).set("tblock", 1)
+    n0 = ctx.launch_count()
+    a, b = u.copy(), np.zeros_like(u)
+    m.run_steps(ctx, "@entry", [b, a], 7)
+    assert ctx.launch_count() - n0 == 7      # one kernel per sweep
+    assert H.bits_equal(b, H.oracle_steps(text, u, [], 7))
     m.destroy()
 
 
@@ -394,7 +417,7 @@ def test_temporal_blocking_bit_exact(nb, ctx, name, shape, ty, steps):
             try:
                 st.set("variant", tbv)
             except nb.NeptuneError:
-                assert tbv.startswith(("tb2m:", "tb2g:", "tb2p:")) and name == "weighted_3d27"   # z-marching needs centre-column z taps
+                assert tbv.startswith(("tb2m:", "tb2g:", "tb2p:", "tb2q:")) and name == "weighted_3d27"   # z-marching needs centre-column z taps
                 continue
             ran.append(tbv)
             fa, fb = nb.Field.from_numpy(ctx, u), nb.Field.from_numpy(ctx, u)
@@ -816,3 +839,125 @@ def test_temporally_blocked_kernels_repeat_bitwise(nb, ctx, name, shape, variant
             f.free()
     finally:
         m.destroy()
+
+
+def test_jit_seven_point_with_permuted_taps_runs_on_every_kernel_family(nb, ctx):
+    """A 7-point body whose taps come in another order than any catalogue file (so: another structure key).  The
+    NVRTC path compiles the hand-written kernels for it: every single-step variant and the temporally blocked
+    z-marchers must reproduce the oracle bit for bit — the body's own association order, not the catalogue's."""
+    shape = (40, 48, 264)
+    offs = [(0, 0, 1), (0, -1, 0), (1, 0, 0), (0, 0, 0), (-1, 0, 0), (0, 1, 0), (0, 0, -1)]
+    text = H.mb.weighted_const(list(shape), offs, [0.11, 0.13, 0.07, 0.4, 0.09, 0.05, 0.15])
+    m = nb.Module(text)
+    assert not nb.runtime.body_compiled(m.apply_desc(0).key())
+    u, _ = H.inputs(shape, 0, "f64", seed=11)
+    want1 = H.oracle_entry(text, u, [])
+    want6 = H.oracle_steps(text, u, [], 6)
+    try:
+        st = m.stencil(ctx, 0)          # first use: NVRTC (or the on-disk JIT cache)
+        names = st.variants()
+        assert "direct" in names and "tma:64x16" in names
+        for v in names:
+            st.set("variant", v)
+            out = np.full_like(u, np.nan)
+            m.run(ctx, "@entry", [out, u])
+            assert st.variant() == v and H.bits_equal(out, want1), v
+        st.set("variant", "auto")
+        for tbv in ["tb2:64x16", "tb2m:128x14", "tb2q:128x14"]:
+            st.set("variant", tbv)
+            fa, fb = nb.Field.from_numpy(ctx, u), nb.Field.from_numpy(ctx, u)
+            r = st.run_steps(fa, fb, [], 6)
+            assert st.variant() == tbv and H.bits_equal(r.download(), want6), tbv
+            fa.free(); fb.free()
+    finally:
+        m.destroy()
+
+
+def test_jit_two_dimensional_body_takes_the_row_marchers(nb, ctx):
+    shape = (96, 1040)
+    offs = [(1, 0), (0, 0), (0, -1), (-1, 0), (0, 1)]
+    text = H.mb.weighted_const(list(shape), offs, [0.2, 0.3, 0.1, 0.25, 0.15])
+    m = nb.Module(text)
+    assert not nb.runtime.body_compiled(m.apply_desc(0).key())
+    u, _ = H.inputs(shape, 0, "f64", seed=12)
+    try:
+        out = np.full_like(u, np.nan)
+        m.run(ctx, "@entry", [out, u])
+        st = m.stencil(ctx, 0)
+        assert st.variant().startswith("rows:"), st.variant()
+        assert H.bits_equal(out, H.oracle_entry(text, u, []))
+        a, b = u.copy(), np.zeros_like(u)
+        res = m.run_steps(ctx, "@entry", [b, a], 8)
+        assert st.variant().startswith("tb2r:"), st.variant()
+        assert H.bits_equal([b, a][res], H.oracle_steps(text, u, [], 8))
+    finally:
+        m.destroy()
+
+
+@pytest.mark.parametrize("ty", ["f64", "f32"])
+def test_jacobi_1000_iterations_bit_exact(nb, ctx, ty):
+    """BASELINE configs[4]'s iteration count at reduced size: 1000 Jacobi iterations with a right-hand side, fused in
+    pairs by the entry's time loop, against the oracle's 1000-step loop, bitwise."""
+    shape = (64, 64, 64)
+    text, n_extra = H.program("jacobi_star", list(shape), ty)
+    u, extra = H.inputs(shape, n_extra, ty, seed=1000)
+    want = H.oracle_steps(text, u, extra, 1000)
+    m = nb.Module(text)
+    try:
+        a, b = u.copy(), np.zeros_like(u)
+        res = m.run_steps(ctx, "@entry", [b, a] + extra, 1000)
+        assert m.stencil(ctx, 0).variant().startswith("tb2")
+        assert H.bits_equal([b, a][res], want)
+    finally:
+        m.destroy()
+
+
+def test_memref_descriptor_entry_points(nb, ctx):
+    """neptune_rt_apply_memref_{1,2,3}d — what generated code calls — on MLIR memref descriptors with a non-zero
+    offset: cached stencil + fields, pipelined upload | sweep | download, bit-exact; repeated calls reuse the cache."""
+    import ctypes as C
+
+    classes = {}
+
+    def memref(rank, buf, offset, shape):
+        if rank not in classes:
+            class M(C.Structure):
+                _fields_ = [("allocated", C.c_void_p), ("aligned", C.c_void_p), ("offset", C.c_int64),
+                            ("sizes", C.c_int64 * rank), ("strides", C.c_int64 * rank)]
+            classes[rank] = M
+        m = classes[rank]()
+        m.allocated = m.aligned = buf.ctypes.data
+        m.offset = offset
+        st = 1
+        for d in reversed(range(rank)):
+            m.sizes[d] = shape[d]
+            m.strides[d] = st
+            st *= shape[d]
+        return m
+
+    L = nb.runtime.lib()
+    for name, shape in [("laplacian_s_1d", (64,)), ("heat_box_2d9", (40, 96)), ("heat_star", (24, 32, 64)), ("jacobi_star", (16, 24, 64))]:
+        text, n_extra = H.program(name, list(shape))
+        u, extra = H.inputs(shape, n_extra, "f64", seed=21)
+        want = H.oracle_entry(text, u, extra)
+        m = nb.Module(text)
+        d = m.apply_desc(0)
+        rank = len(shape)
+        pad = 5                                           # elements before the data: descriptor offset
+        bufs = []
+        for a in [u] + extra:
+            b = np.full(a.size + pad, np.nan)
+            b[pad:] = a.ravel()
+            bufs.append(b)
+        outb = np.full(u.size + pad, np.nan)
+        first = memref(rank, bufs[0], pad, shape)
+        ins = (type(first) * len(bufs))(*[memref(rank, b, pad, shape) for b in bufs])
+        om = memref(rank, outb, pad, shape)
+        fn = getattr(L, "neptune_rt_apply_memref_%dd" % rank)
+        for rep in range(2):
+            outb[:] = np.nan
+            fn(C.byref(d.c()), len(bufs), C.cast(ins, C.c_void_p), C.cast(C.byref(om), C.c_void_p))
+            assert np.isnan(outb[:pad]).all()
+            assert H.bits_equal(outb[pad:].reshape(shape), want), name
+        m.destroy()
+    L.neptune_rt_memref_cache_clear()

@@ -114,3 +114,49 @@ def test_sweep_then_reduce_program():
     s2 = oc.CompiledModule(text, tag="t_sweep_reduce").call_scalar("@entry", [o2, u])
     assert H.bits_equal(o1, o2) and float(s1) == s2
     assert H.bits_equal(o1, H.oracle_entry(H.mb.heat_star([9, 12, 14], 0.1), u, []))
+
+
+# ---- third restatement: the loop nest as LLVM IR, compiled by LLVM (oracle/llvm_lowering.py) ------------------
+LLVM_CASES = [("heat_star", (12, 16, 20), "f64"), ("heat_star", (24, 32), "f64"), ("heat_star", (24, 32), "f32"),
+              ("heat_star", (40,), "f64"), ("heat_box_2d9", (24, 32), "f64"), ("jacobi_star", (10, 12, 16), "f64"),
+              ("jacobi_star", (10, 12, 16), "f32"), ("varcoef_3d27", (8, 10, 12), "f64"), ("varcoef_3d7", (8, 10, 12), "f64"),
+              ("weighted_3d27", (8, 9, 10), "f64"), ("weighted_2d9", (16, 20), "f64"), ("euler_opdef", (10, 12, 16), "f64"),
+              ("laplacian_s_1d", (16,), "f64")]
+
+
+@pytest.mark.parametrize("name,shape,ty", LLVM_CASES, ids=["%s-%s-%s" % (n, "x".join(map(str, s)), t) for n, s, t in LLVM_CASES])
+def test_llvm_restatement_equals_numpy_restatement(name, shape, ty):
+    """fmul/fadd without fast-math flags on the generic x86-64 CPU, JIT-compiled by LLVM 20 (the closest analogue of the
+    reference's mlir-translate + llc flow, smoke_apply.sh:22-29) == the numpy slices, bit for bit, over several steps."""
+    from oracle import llvm_lowering as oll
+    text, n_extra = H.program(name, list(shape), ty)
+    u, extra = H.inputs(shape, n_extra, ty, seed=17)
+    a = H.oracle_steps(text, u, extra, 4)
+    b = oll.run_steps(ms.parse(text), u, extra, 4)
+    assert H.bits_equal(a, b)
+
+
+def test_llvm_restatement_emits_no_fused_multiply_add():
+    from oracle import llvm_lowering as oll
+    text, _ = H.program("heat_star", [12, 16, 20])
+    ap = [op.apply for op in ms.parse(text).functions["@entry"].ops if op.name == "apply"][0]
+    la = oll.LlvmApply(ap)
+    assert "fmul double" in la.ir and "fadd double" in la.ir and "fast" not in la.ir and "contract" not in la.ir
+    asm = la.asm.lower()
+    assert "vfmadd" not in asm and "fma" not in asm and "mulsd" in asm and "addsd" in asm
+
+
+def test_llvm_restatement_on_the_reference_fixtures():
+    import json
+    import os
+    from oracle import llvm_lowering as oll
+    pack = json.load(open(os.path.join(os.path.dirname(__file__), "golden", "reference_inputs.json")))
+    for c in pack["cases"]:
+        if c["text"] != "verbatim":
+            continue
+        mod = ms.parse(pack["files"][c["file"]]["text"])
+        x = np.array([float.fromhex(v) for v in c["input"]])
+        for want in c["outputs"]:
+            y = oll.run_function(mod, c["function"], [x])[0]
+            assert H.bits_equal(np.asarray(y), np.array([float.fromhex(v) for v in want])), c["function"]
+            x = np.array(y, copy=True)
