@@ -263,6 +263,34 @@ void neptune_rt_apply_memref(const neptune_rt_stencil_desc *desc, int n_in,
 /* Releases the stencils and device fields the memref entry points cached. */
 void neptune_rt_memref_cache_clear(void);
 
+/* ---- what the MLIR pass emits (mlir/lib/Passes/ApplyToB200.cpp) --------------------------- */
+/* A descriptor as one position-independent byte string: the pass packs it at compile time and stores the bytes in
+ * an llvm.mlir.global constant (a struct with pointers would need relocations in a constant global). Returns the
+ * number of bytes the packed form takes; writes it when `capacity` suffices. Pure host code. */
+int64_t neptune_rt_desc_pack(const neptune_rt_stencil_desc *desc, void *buf, int64_t capacity);
+/* The call builder: an apply has a variable number of operands, a C function has not, so generated code makes
+ *     %c = call @neptune_rt_call_begin(%desc_global, %bytes)
+ *     call @neptune_rt_call_input_<rank>d(%c, k, %operand_k)          once per operand
+ *     call @neptune_rt_call_run_<rank>d(%c, %result)                  result buffer allocated by the caller
+ * with the functions declared `llvm.emit_c_interface`, so that func-to-llvm passes every memref as a pointer to its
+ * descriptor; the `_mlir_ciface_` names that lowering produces are exported beside the plain ones. The call object
+ * is cached per descriptor global; sweeps run through neptune_rt_apply_memref's cached, pipelined path. Aborts on
+ * failure like the reference's shims (NeptunePETScRuntime.cpp:15-30). One host thread. */
+void *neptune_rt_call_begin(const void *packed_desc, int64_t bytes);
+void neptune_rt_call_input_1d(void *call, int32_t k, const neptune_rt_memref_1d *operand);
+void neptune_rt_call_input_2d(void *call, int32_t k, const neptune_rt_memref_2d *operand);
+void neptune_rt_call_input_3d(void *call, int32_t k, const neptune_rt_memref_3d *operand);
+void neptune_rt_call_run_1d(void *call, const neptune_rt_memref_1d *result);
+void neptune_rt_call_run_2d(void *call, const neptune_rt_memref_2d *result);
+void neptune_rt_call_run_3d(void *call, const neptune_rt_memref_3d *result);
+void *_mlir_ciface_neptune_rt_call_begin(const void *packed_desc, int64_t bytes);
+void _mlir_ciface_neptune_rt_call_input_1d(void *call, int32_t k, const neptune_rt_memref_1d *operand);
+void _mlir_ciface_neptune_rt_call_input_2d(void *call, int32_t k, const neptune_rt_memref_2d *operand);
+void _mlir_ciface_neptune_rt_call_input_3d(void *call, int32_t k, const neptune_rt_memref_3d *operand);
+void _mlir_ciface_neptune_rt_call_run_1d(void *call, const neptune_rt_memref_1d *result);
+void _mlir_ciface_neptune_rt_call_run_2d(void *call, const neptune_rt_memref_2d *result);
+void _mlir_ciface_neptune_rt_call_run_3d(void *call, const neptune_rt_memref_3d *result);
+
 #ifdef __cplusplus
 }
 #endif

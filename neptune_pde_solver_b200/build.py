@@ -116,6 +116,14 @@ def build(verbose: bool = False, jobs: int | None = None) -> str:
     if not (os.path.exists(LIB) and os.path.exists(link_stamp) and open(link_stamp).read() == want):
         _run([NVCC] + ARCH + ["-shared", "-o", LIB] + objs + ["-ldl", "-lpthread"], verbose)
         open(link_stamp, "w").write(want)
+    # 5. neptune-opt-b200: the neptune-opt-shaped driver (csrc/tools/neptune_opt_b200.cpp), linked against the library
+    opt_exe = os.path.join(LIBDIR, "neptune-opt-b200")
+    opt_src = os.path.join(CSRC, "tools", "neptune_opt_b200.cpp")
+    stamp = opt_exe + ".stamp"
+    want = _digest([opt_src, LIB] + sorted(glob.glob(os.path.join(INCLUDE, "*.h"))))
+    if not (os.path.exists(opt_exe) and os.path.exists(stamp) and open(stamp).read() == want):
+        _run([CXX] + CXX_FLAGS + [opt_src, "-o", opt_exe, "-L", LIBDIR, "-lneptune_rt_b200", "-Wl,-rpath,$ORIGIN"], verbose)
+        open(stamp, "w").write(want)
     return LIB
 
 

@@ -20,6 +20,7 @@
 #include <cstring>
 #include <functional>
 #include <initializer_list>
+#include <memory>
 #include <string>
 #include <vector>
 
@@ -1505,3 +1506,128 @@ extern "C" void neptune_rt_memref_cache_clear(void) {
   }
   memref_cache().clear();
 }
+
+// ---------------------------------------------------------------------------------------------
+// packed descriptors + the call builder (what the MLIR pass of mlir/lib/Passes/ApplyToB200.cpp emits calls to)
+// ---------------------------------------------------------------------------------------------
+// A neptune_rt_stencil_desc holds pointers, which a compiler cannot put into a constant global without
+// relocations; the pass therefore stores the descriptor as a flat, position-independent byte string
+// (neptune_rt_desc_pack) in an llvm.mlir.global and hands that to the runtime.
+namespace {
+struct PackedHeader {
+  uint32_t magic, version;
+  int32_t rank, dtype, n_inputs, n_ops, yield_value, flags;
+  int64_t lb[3], ub[3], out_lb[3], out_ub[3];
+};
+constexpr uint32_t PACK_MAGIC = 0x4e423230u;   // "NB20"
+
+struct UnpackedDesc {
+  neptune_rt_stencil_desc d;
+  std::vector<neptune_rt_body_op> ops;
+  std::vector<int64_t> in_lb, in_ub;
+};
+
+bool unpack_desc(const void *blob, int64_t bytes, UnpackedDesc &u) {
+  if (!blob || bytes < (int64_t)sizeof(PackedHeader)) return false;
+  PackedHeader h;
+  std::memcpy(&h, blob, sizeof h);
+  if (h.magic != PACK_MAGIC || h.version != 1 || h.rank < 1 || h.rank > 3 || h.n_inputs < 1 || h.n_inputs > NEPTUNE_RT_MAX_INPUTS || h.n_ops < 1 || h.n_ops > 4096) return false;
+  const size_t nb = (size_t)h.n_inputs * h.rank;
+  const size_t need = sizeof h + 2 * nb * sizeof(int64_t) + (size_t)h.n_ops * sizeof(neptune_rt_body_op);
+  if ((size_t)bytes < need) return false;
+  const char *p = (const char *)blob + sizeof h;
+  u.in_lb.resize(nb); u.in_ub.resize(nb); u.ops.resize((size_t)h.n_ops);
+  std::memcpy(u.in_lb.data(), p, nb * sizeof(int64_t)); p += nb * sizeof(int64_t);
+  std::memcpy(u.in_ub.data(), p, nb * sizeof(int64_t)); p += nb * sizeof(int64_t);
+  std::memcpy(u.ops.data(), p, (size_t)h.n_ops * sizeof(neptune_rt_body_op));
+  neptune_rt_stencil_desc &d = u.d;
+  std::memset(&d, 0, sizeof d);
+  d.rank = h.rank; d.dtype = h.dtype; d.n_inputs = h.n_inputs; d.n_ops = h.n_ops; d.yield_value = h.yield_value; d.flags = h.flags;
+  for (int k = 0; k < 3; ++k) { d.lb[k] = h.lb[k]; d.ub[k] = h.ub[k]; d.out_lb[k] = h.out_lb[k]; d.out_ub[k] = h.out_ub[k]; }
+  d.ops = u.ops.data(); d.in_lb = u.in_lb.data(); d.in_ub = u.in_ub.data();
+  return true;
+}
+
+struct PendingCall {
+  const void *blob = nullptr;
+  std::unique_ptr<UnpackedDesc> desc;
+  const void *in_host[NEPTUNE_RT_MAX_INPUTS] = {};
+};
+std::vector<std::unique_ptr<PendingCall>> &call_cache() {   // one per descriptor global (keyed by its address)
+  static std::vector<std::unique_ptr<PendingCall>> v;
+  return v;
+}
+}  // namespace
+
+extern "C" int64_t neptune_rt_desc_pack(const neptune_rt_stencil_desc *d, void *buf, int64_t capacity) {
+  if (!d || d->rank < 1 || d->rank > 3 || d->n_inputs < 1 || d->n_ops < 1) return -1;
+  const size_t nb = (size_t)d->n_inputs * d->rank;
+  const size_t need = sizeof(PackedHeader) + 2 * nb * sizeof(int64_t) + (size_t)d->n_ops * sizeof(neptune_rt_body_op);
+  if (!buf || capacity < (int64_t)need) return (int64_t)need;
+  PackedHeader h;
+  std::memset(&h, 0, sizeof h);
+  h.magic = PACK_MAGIC; h.version = 1;
+  h.rank = d->rank; h.dtype = d->dtype; h.n_inputs = d->n_inputs; h.n_ops = d->n_ops; h.yield_value = d->yield_value; h.flags = d->flags;
+  for (int k = 0; k < d->rank; ++k) { h.lb[k] = d->lb[k]; h.ub[k] = d->ub[k]; h.out_lb[k] = d->out_lb[k]; h.out_ub[k] = d->out_ub[k]; }
+  char *p = (char *)buf;
+  std::memcpy(p, &h, sizeof h); p += sizeof h;
+  std::memcpy(p, d->in_lb, nb * sizeof(int64_t)); p += nb * sizeof(int64_t);
+  std::memcpy(p, d->in_ub, nb * sizeof(int64_t)); p += nb * sizeof(int64_t);
+  for (int i = 0; i < d->n_ops; ++i) {   // field by field: padding bytes of the struct stay zero, the blob is reproducible
+    neptune_rt_body_op o;
+    std::memset(&o, 0, sizeof o);
+    o.opcode = d->ops[i].opcode; o.a = d->ops[i].a; o.b = d->ops[i].b; o.input = d->ops[i].input;
+    for (int k = 0; k < 3; ++k) o.offset[k] = d->ops[i].offset[k];
+    o.value = d->ops[i].value;
+    std::memcpy(p, &o, sizeof o); p += sizeof o;
+  }
+  return (int64_t)need;
+}
+
+extern "C" void *neptune_rt_call_begin(const void *packed_desc, int64_t bytes) {
+  neptune_rt_ctx *c = default_ctx();
+  for (auto &pc : call_cache())
+    if (pc->blob == packed_desc) return pc.get();
+  std::unique_ptr<PendingCall> pc(new PendingCall());
+  pc->blob = packed_desc;
+  pc->desc.reset(new UnpackedDesc());
+  if (!unpack_desc(packed_desc, bytes, *pc->desc)) { set_error(c, NEPTUNE_RT_EINVAL, "malformed packed stencil descriptor"); memref_die(c, "neptune_rt_call_begin"); }
+  call_cache().push_back(std::move(pc));
+  return call_cache().back().get();
+}
+
+namespace {
+template <int R, class M> void call_input(void *call, int32_t k, const M *m) {
+  neptune_rt_ctx *c = default_ctx();
+  PendingCall *pc = (PendingCall *)call;
+  if (!pc || !m || k < 0 || k >= pc->desc->d.n_inputs || pc->desc->d.rank != R) { set_error(c, NEPTUNE_RT_EINVAL, "bad call-builder input %d", (int)k); memref_die(c, "neptune_rt_call_input"); }
+  const neptune_rt_stencil_desc &d = pc->desc->d;
+  pc->in_host[k] = memref_host_ptr<R>(c, *m, d.dtype, d.in_lb + (size_t)k * R, d.in_ub + (size_t)k * R, "input memref");
+}
+template <int R, class M> void call_run(void *call, const M *out) {
+  neptune_rt_ctx *c = default_ctx();
+  PendingCall *pc = (PendingCall *)call;
+  if (!pc || !out || pc->desc->d.rank != R) { set_error(c, NEPTUNE_RT_EINVAL, "bad call-builder result"); memref_die(c, "neptune_rt_call_run"); }
+  const neptune_rt_stencil_desc &d = pc->desc->d;
+  for (int k = 0; k < d.n_inputs; ++k)
+    if (!pc->in_host[k]) { set_error(c, NEPTUNE_RT_EINVAL, "input %d of the apply was never bound", k); memref_die(c, "neptune_rt_call_run"); }
+  void *op = const_cast<void *>(memref_host_ptr<R>(c, *out, d.dtype, d.out_lb, d.out_ub, "result memref"));
+  apply_memref_ptrs(&d, d.n_inputs, pc->in_host, op);
+  for (int k = 0; k < d.n_inputs; ++k) pc->in_host[k] = nullptr;
+}
+}  // namespace
+
+extern "C" void neptune_rt_call_input_1d(void *call, int32_t k, const neptune_rt_memref_1d *m) { call_input<1>(call, k, m); }
+extern "C" void neptune_rt_call_input_2d(void *call, int32_t k, const neptune_rt_memref_2d *m) { call_input<2>(call, k, m); }
+extern "C" void neptune_rt_call_input_3d(void *call, int32_t k, const neptune_rt_memref_3d *m) { call_input<3>(call, k, m); }
+extern "C" void neptune_rt_call_run_1d(void *call, const neptune_rt_memref_1d *out) { call_run<1>(call, out); }
+extern "C" void neptune_rt_call_run_2d(void *call, const neptune_rt_memref_2d *out) { call_run<2>(call, out); }
+extern "C" void neptune_rt_call_run_3d(void *call, const neptune_rt_memref_3d *out) { call_run<3>(call, out); }
+// the names func-to-llvm gives the C-interface wrappers of functions declared with `llvm.emit_c_interface`
+extern "C" void *_mlir_ciface_neptune_rt_call_begin(const void *b, int64_t n) { return neptune_rt_call_begin(b, n); }
+extern "C" void _mlir_ciface_neptune_rt_call_input_1d(void *c, int32_t k, const neptune_rt_memref_1d *m) { call_input<1>(c, k, m); }
+extern "C" void _mlir_ciface_neptune_rt_call_input_2d(void *c, int32_t k, const neptune_rt_memref_2d *m) { call_input<2>(c, k, m); }
+extern "C" void _mlir_ciface_neptune_rt_call_input_3d(void *c, int32_t k, const neptune_rt_memref_3d *m) { call_input<3>(c, k, m); }
+extern "C" void _mlir_ciface_neptune_rt_call_run_1d(void *c, const neptune_rt_memref_1d *o) { call_run<1>(c, o); }
+extern "C" void _mlir_ciface_neptune_rt_call_run_2d(void *c, const neptune_rt_memref_2d *o) { call_run<2>(c, o); }
+extern "C" void _mlir_ciface_neptune_rt_call_run_3d(void *c, const neptune_rt_memref_3d *o) { call_run<3>(c, o); }

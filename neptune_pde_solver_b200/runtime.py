@@ -115,6 +115,21 @@ def lib() -> C.CDLL:
         "neptune_rt_apply_memref_2d": (None, [C.POINTER(StencilDescC), i32, vp, vp]),
         "neptune_rt_apply_memref_3d": (None, [C.POINTER(StencilDescC), i32, vp, vp]),
         "neptune_rt_memref_cache_clear": (None, []),
+        "neptune_rt_desc_pack": (i64, [C.POINTER(StencilDescC), vp, i64]),
+        "neptune_rt_call_begin": (vp, [vp, i64]),
+        "neptune_rt_call_input_1d": (None, [vp, i32, vp]),
+        "neptune_rt_call_input_2d": (None, [vp, i32, vp]),
+        "neptune_rt_call_input_3d": (None, [vp, i32, vp]),
+        "neptune_rt_call_run_1d": (None, [vp, vp]),
+        "neptune_rt_call_run_2d": (None, [vp, vp]),
+        "neptune_rt_call_run_3d": (None, [vp, vp]),
+        "_mlir_ciface_neptune_rt_call_begin": (vp, [vp, i64]),
+        "_mlir_ciface_neptune_rt_call_input_1d": (None, [vp, i32, vp]),
+        "_mlir_ciface_neptune_rt_call_input_2d": (None, [vp, i32, vp]),
+        "_mlir_ciface_neptune_rt_call_input_3d": (None, [vp, i32, vp]),
+        "_mlir_ciface_neptune_rt_call_run_1d": (None, [vp, vp]),
+        "_mlir_ciface_neptune_rt_call_run_2d": (None, [vp, vp]),
+        "_mlir_ciface_neptune_rt_call_run_3d": (None, [vp, vp]),
         "neptune_b200_compile": (i32, [C.c_char_p, C.c_char_p, C.POINTER(vp), C.c_char_p, C.c_size_t]),
         "neptune_b200_module_destroy": (i32, [vp]),
         "neptune_b200_apply_count": (i32, [vp]),

@@ -959,5 +959,21 @@ def test_memref_descriptor_entry_points(nb, ctx):
             fn(C.byref(d.c()), len(bufs), C.cast(ins, C.c_void_p), C.cast(C.byref(om), C.c_void_p))
             assert np.isnan(outb[:pad]).all()
             assert H.bits_equal(outb[pad:].reshape(shape), want), name
+        # the call sequence the MLIR pass emits (mlir/lib/Passes/ApplyToB200.cpp): packed descriptor in a "global",
+        # call_begin, one call_input per operand, call_run — through the _mlir_ciface_ names func-to-llvm produces
+        dc = d.c()
+        need = L.neptune_rt_desc_pack(C.byref(dc), None, 0)
+        blob = C.create_string_buffer(need)
+        assert L.neptune_rt_desc_pack(C.byref(dc), blob, need) == need
+        blob2 = C.create_string_buffer(need)
+        L.neptune_rt_desc_pack(C.byref(d.c()), blob2, need)
+        assert blob.raw == blob2.raw                      # reproducible bytes (padding zeroed)
+        for rep in range(2):
+            outb[:] = np.nan
+            call = L._mlir_ciface_neptune_rt_call_begin(blob, need)
+            for k in range(len(bufs)):
+                getattr(L, "_mlir_ciface_neptune_rt_call_input_%dd" % rank)(call, k, C.cast(C.byref(ins[k]), C.c_void_p))
+            getattr(L, "_mlir_ciface_neptune_rt_call_run_%dd" % rank)(call, C.cast(C.byref(om), C.c_void_p))
+            assert H.bits_equal(outb[pad:].reshape(shape), want), name
         m.destroy()
     L.neptune_rt_memref_cache_clear()
