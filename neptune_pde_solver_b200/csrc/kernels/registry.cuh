@@ -47,231 +47,117 @@ template <class KP> inline bool set_gap(KP &p, const SweepArgs &a, int dim) {
   return true;
 }
 
-template <class F, class C, bool FMA> int launch_tma(const SweepArgs &a) {
+// ---- one launcher for every persistent-item kernel ------------------------------------------------------------
+// A kernel family is described by a traits struct: the geometry (THREADS, SMEM_BYTES, tile), the marching
+// dimension of its work items (0: (z-chunk, column) items; 1: (row-chunk, strip) items of the rank-2 kernels), the
+// halo its items re-read in that dimension, and how the kernel is called.
+template <class F, class C, bool FMA> struct TmaK {
   typedef TmaGeom<F, C> G;
-  auto kernel = sweep_tma<F, C, FMA>;
+  static constexpr int MARCH_DIM = 0, ZHALO = F::RZ, TX = C::TX, TY = C::TY, KIND = VARIANT_TMA, STEPS = 1, GAP_DIM = 0;
+  static constexpr bool TMAP = true;
+  static constexpr int BOX_X = G::SXP, BOX_Y = G::SY, HALO_X = G::HX, HALO_Y = G::RY;
+  static void call(int grid, const KParams<F> &p, const SweepArgs &a) { sweep_tma<F, C, FMA><<<grid, G::THREADS, G::SMEM_BYTES, a.stream>>>(p, *a.tmap); }
+  static const void *fn() { return (const void *)sweep_tma<F, C, FMA>; }
+};
+template <class F, class C, bool FMA> struct Tb2K {        // both levels through shared memory (narrow boxes)
+  typedef Tb2Geom<F, C> G;
+  static constexpr int MARCH_DIM = 0, ZHALO = 2, TX = C::TX, TY = C::TY, KIND = VARIANT_TB2, STEPS = 2, GAP_DIM = 0;
+  static constexpr bool TMAP = true;
+  static constexpr int BOX_X = G::P0, BOX_Y = G::BOX_Y, HALO_X = 2 * G::VX, HALO_Y = 2;
+  static void call(int grid, const KParams<F> &p, const SweepArgs &a) { sweep_tb2<F, C, FMA><<<grid, G::THREADS, G::SMEM_BYTES, a.stream>>>(p, *a.tmap); }
+  static const void *fn() { return (const void *)sweep_tb2<F, C, FMA>; }
+};
+template <class F, class C, bool FMA> struct Tb2mK {       // z-marching; thin launches and bodies with a pointwise input
+  typedef Tb2mGeom<F, C> G;
+  static constexpr int MARCH_DIM = 0, ZHALO = 2, TX = C::TX, TY = C::TY, KIND = VARIANT_TB2, STEPS = 2, GAP_DIM = 0;
+  static constexpr bool TMAP = true;
+  static constexpr int BOX_X = G::P0, BOX_Y = G::BOX_Y, HALO_X = 2 * G::VX, HALO_Y = 2;
+  static void call(int grid, const KParams<F> &p, const SweepArgs &a) {
+    sweep_tb2m<F, C, FMA><<<grid, G::THREADS, G::SMEM_BYTES, a.stream>>>(p, *a.tmap, a.tmap_pw ? *a.tmap_pw : *a.tmap);
+  }
+  static const void *fn() { return (const void *)sweep_tb2m<F, C, FMA>; }
+};
+template <class F, class C, bool FMA> struct Tb2qK {       // z-marching, grouped, software-pipelined, lean steady state
+  typedef Tb2qGeom<F, C> G;
+  static constexpr int MARCH_DIM = 0, ZHALO = 2, TX = C::TX, TY = C::TY, KIND = VARIANT_TB2, STEPS = 2, GAP_DIM = 0;
+  static constexpr bool TMAP = true;
+  static constexpr int BOX_X = G::P0, BOX_Y = G::BOX_Y, HALO_X = 2 * G::VX, HALO_Y = 2;
+  static void call(int grid, const KParams<F> &p, const SweepArgs &a) { sweep_tb2q<F, C, FMA><<<grid, G::THREADS, G::SMEM_BYTES, a.stream>>>(p, *a.tmap); }
+  static const void *fn() { return (const void *)sweep_tb2q<F, C, FMA>; }
+};
+template <class F, class C, bool FMA> struct RowsK {       // rank 2: strip of TX columns marched down the rows
+  typedef RowGeom<F, C> G;
+  static constexpr int MARCH_DIM = 1, ZHALO = 1, TX = C::TX, TY = C::RB, KIND = VARIANT_ROWS, STEPS = 1, GAP_DIM = 1;
+  static constexpr bool TMAP = false;
+  static constexpr int BOX_X = 0, BOX_Y = 0, HALO_X = G::HX, HALO_Y = 1;
+  static void call(int grid, const KParams<F> &p, const SweepArgs &a) { sweep_rows<F, C, FMA><<<grid, G::THREADS, G::SMEM_BYTES, a.stream>>>(p); }
+  static const void *fn() { return (const void *)sweep_rows<F, C, FMA>; }
+};
+template <class F, class C, bool FMA> struct Rows2K {      // rank 2, two time steps per launch
+  typedef Rows2Geom<F, C> G;
+  static constexpr int MARCH_DIM = 1, ZHALO = 2, TX = G::TX, TY = C::RB, KIND = VARIANT_TB2, STEPS = 2, GAP_DIM = 1;
+  static constexpr bool TMAP = false;
+  static constexpr int BOX_X = 0, BOX_Y = 0, HALO_X = 2 * G::VX, HALO_Y = 2;
+  static void call(int grid, const KParams<F> &p, const SweepArgs &a) { sweep_rows2<F, C, FMA><<<grid, G::THREADS, G::SMEM_BYTES, a.stream>>>(p); }
+  static const void *fn() { return (const void *)sweep_rows2<F, C, FMA>; }
+};
+
+template <class F, class K> int launch_items(const SweepArgs &a) {
+  typedef typename K::G G;
   static int occ_cached[16] = {0};
   int dev = 0;
   cudaGetDevice(&dev);
   if (dev < 0 || dev >= 16) dev = 0;
   if (occ_cached[dev] == 0) {
-    cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, G::SMEM_BYTES);
+    cudaError_t e = cudaFuncSetAttribute(K::fn(), cudaFuncAttributeMaxDynamicSharedMemorySize, G::SMEM_BYTES);
     if (e != cudaSuccess) return (int)e;
     int occ = 0;
-    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kernel, G::THREADS, G::SMEM_BYTES);
+    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, K::fn(), G::THREADS, G::SMEM_BYTES);
     if (e != cudaSuccess) return (int)e;
     if (occ < 1) return (int)cudaErrorLaunchOutOfResources;
     occ_cached[dev] = occ;
   }
-  if (!a.tmap) return (int)cudaErrorInvalidValue;
+  if (K::TMAP && !a.tmap) return (int)cudaErrorInvalidValue;
+  if (K::TMAP && F::NIN > 1 && K::KIND == VARIANT_TB2 && !a.tmap_pw) return (int)cudaErrorInvalidValue;
   KParams<F> p;
   fill_params<F>(p, a);
-  const int wz = a.whi[0] - a.wlo[0];
-  if (wz <= 0 || a.whi[1] <= a.wlo[1] || a.whi[2] <= a.wlo[2]) return 0;
-  p.cxo = a.wlo[2] / C::TX;
-  p.cyo = a.wlo[1] / C::TY;
-  p.ncx = (a.whi[2] + C::TX - 1) / C::TX - p.cxo;
-  p.ncy = (a.whi[1] + C::TY - 1) / C::TY - p.cyo;
+  constexpr int M = K::MARCH_DIM;
+  const int planes = a.whi[M] - a.wlo[M];
+  if (a.whi[0] <= a.wlo[0] || a.whi[1] <= a.wlo[1] || a.whi[2] <= a.wlo[2]) return 0;
+  p.cxo = a.wlo[2] / K::TX;
+  p.ncx = (a.whi[2] + K::TX - 1) / K::TX - p.cxo;
+  p.cyo = 0;
+  p.ncy = 1;
+  if (M == 0) {
+    p.cyo = a.wlo[1] / K::TY;
+    p.ncy = (a.whi[1] + K::TY - 1) / K::TY - p.cyo;
+  }
   const int ncols = p.ncx * p.ncy;
   const int slots = a.sm_count * occ_cached[dev];
-  p.zchunk = a.zchunk > 0 ? std::min(a.zchunk, wz) : choose_zchunk(wz, ncols, slots, F::RZ);
-  p.nchunks = (wz + p.zchunk - 1) / p.zchunk;
-  if (!set_gap(p, a, 0)) return (int)cudaErrorInvalidValue;
+  p.zchunk = a.zchunk > 0 ? std::min(a.zchunk, planes) : choose_zchunk(planes, ncols, slots, K::ZHALO);
+  p.nchunks = (planes + p.zchunk - 1) / p.zchunk;
+  if (!set_gap(p, a, M)) return (int)cudaErrorInvalidValue;
   const long long items = (long long)p.nchunks * ncols;
   if (items > 0x7fffffffLL) return (int)cudaErrorInvalidConfiguration;
   p.nitems = (int)items;
-  const int grid = (int)std::min<long long>(items, slots);
-  kernel<<<grid, G::THREADS, G::SMEM_BYTES, a.stream>>>(p, *a.tmap);
+  K::call((int)std::min<long long>(items, slots), p, a);
   return (int)cudaGetLastError();
 }
 
-// MARCH: 0 = sweep_tb2 (both levels through shared memory), 1 = sweep_tb2m (z-marching), 2 = sweep_tb2g (z-marching,
-// grouped), 3 = sweep_tb2p (grouped, phase B software-pipelined into phase A), 4 = sweep_tb2q (tb2p with a lean steady state)
-template <class F, class C, int MARCH> struct Tb2GeomOf { typedef Tb2Geom<F, C> type; };
-template <class F, class C> struct Tb2GeomOf<F, C, 1> { typedef Tb2mGeom<F, C> type; };
-template <class F, class C> struct Tb2GeomOf<F, C, 2> { typedef Tb2gGeom<F, C> type; };
-template <class F, class C> struct Tb2GeomOf<F, C, 3> { typedef Tb2pGeom<F, C> type; };
-template <class F, class C> struct Tb2GeomOf<F, C, 4> { typedef Tb2qGeom<F, C> type; };
-
-template <class F, class C, bool FMA, int MARCH = 0> int launch_tb2(const SweepArgs &a) {
-  typedef typename Tb2GeomOf<F, C, MARCH>::type G;
-  auto kernel = [] {
-    if constexpr (MARCH == 1) return sweep_tb2m<F, C, FMA>;
-    else if constexpr (MARCH == 2) return sweep_tb2g<F, C, FMA>;
-    else if constexpr (MARCH == 3) return sweep_tb2p<F, C, FMA>;
-    else if constexpr (MARCH == 4) return sweep_tb2q<F, C, FMA>;
-    else return sweep_tb2<F, C, FMA>;
-  }();
-  static int occ_cached[16] = {0};
-  int dev = 0;
-  cudaGetDevice(&dev);
-  if (dev < 0 || dev >= 16) dev = 0;
-  if (occ_cached[dev] == 0) {
-    cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, G::SMEM_BYTES);
-    if (e != cudaSuccess) return (int)e;
-    int occ = 0;
-    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kernel, G::THREADS, G::SMEM_BYTES);
-    if (e != cudaSuccess) return (int)e;
-    if (occ < 1) return (int)cudaErrorLaunchOutOfResources;
-    occ_cached[dev] = occ;
-  }
-  if (!a.tmap) return (int)cudaErrorInvalidValue;
-  KParams<F> p;
-  fill_params<F>(p, a);
-  const int wz = a.whi[0] - a.wlo[0];
-  if (wz <= 0 || a.whi[1] <= a.wlo[1] || a.whi[2] <= a.wlo[2]) return 0;
-  p.cxo = a.wlo[2] / C::TX;
-  p.cyo = a.wlo[1] / C::TY;
-  p.ncx = (a.whi[2] + C::TX - 1) / C::TX - p.cxo;
-  p.ncy = (a.whi[1] + C::TY - 1) / C::TY - p.cyo;
-  const int ncols = p.ncx * p.ncy;
-  const int slots = a.sm_count * occ_cached[dev];
-  p.zchunk = a.zchunk > 0 ? std::min(a.zchunk, wz) : choose_zchunk(wz, ncols, slots, 2);
-  p.nchunks = (wz + p.zchunk - 1) / p.zchunk;
-  if (!set_gap(p, a, 0)) return (int)cudaErrorInvalidValue;
-  const long long items = (long long)p.nchunks * ncols;
-  if (items > 0x7fffffffLL) return (int)cudaErrorInvalidConfiguration;
-  p.nitems = (int)items;
-  const int grid = (int)std::min<long long>(items, slots);
-  if constexpr (MARCH == 1) {
-    if (F::NIN > 1 && !a.tmap_pw) return (int)cudaErrorInvalidValue;
-    kernel<<<grid, G::THREADS, G::SMEM_BYTES, a.stream>>>(p, *a.tmap, a.tmap_pw ? *a.tmap_pw : *a.tmap);
-  } else {
-    kernel<<<grid, G::THREADS, G::SMEM_BYTES, a.stream>>>(p, *a.tmap);
-  }
-  return (int)cudaGetLastError();
-}
-
-// rank-2 row marching (sweep_rows.cuh): work item = (row chunk, strip of TX columns)
-template <class F, class C, bool FMA> int launch_rows(const SweepArgs &a) {
-  typedef RowGeom<F, C> G;
-  auto kernel = sweep_rows<F, C, FMA>;
-  static int occ_cached[16] = {0};
-  int dev = 0;
-  cudaGetDevice(&dev);
-  if (dev < 0 || dev >= 16) dev = 0;
-  if (occ_cached[dev] == 0) {
-    cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, G::SMEM_BYTES);
-    if (e != cudaSuccess) return (int)e;
-    int occ = 0;
-    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kernel, G::THREADS, G::SMEM_BYTES);
-    if (e != cudaSuccess) return (int)e;
-    if (occ < 1) return (int)cudaErrorLaunchOutOfResources;
-    occ_cached[dev] = occ;
-  }
-  KParams<F> p;
-  fill_params<F>(p, a);
-  const int wy = a.whi[1] - a.wlo[1];
-  if (wy <= 0 || a.whi[2] <= a.wlo[2]) return 0;
-  p.cxo = a.wlo[2] / C::TX;
-  p.ncx = (a.whi[2] + C::TX - 1) / C::TX - p.cxo;
-  p.ncy = 1;
-  const int slots = a.sm_count * occ_cached[dev];
-  p.zchunk = a.zchunk > 0 ? std::min(a.zchunk, wy) : choose_zchunk(wy, p.ncx, slots, 1);
-  p.nchunks = (wy + p.zchunk - 1) / p.zchunk;
-  if (!set_gap(p, a, 1)) return (int)cudaErrorInvalidValue;
-  const long long items = (long long)p.nchunks * p.ncx;
-  if (items > 0x7fffffffLL) return (int)cudaErrorInvalidConfiguration;
-  p.nitems = (int)items;
-  const int grid = (int)std::min<long long>(items, slots);
-  kernel<<<grid, G::THREADS, G::SMEM_BYTES, a.stream>>>(p);
-  return (int)cudaGetLastError();
-}
-
-template <class F, class C, bool FMA> Variant rows_variant(const char *name) {
-  typedef RowGeom<F, C> G;
+template <class F, class K, bool FMA> Variant item_variant(const char *name) {
+  typedef typename K::G G;
   Variant v;
   v.name = name;
-  v.kind = VARIANT_ROWS;
+  v.kind = K::KIND;
   v.fma = FMA;
-  v.tx = C::TX; v.ty = C::RB;
-  v.halo_x = G::HX; v.halo_y = 1;
+  v.steps = K::STEPS;
+  v.needs_tmap = K::TMAP;
+  v.tx = K::TX; v.ty = K::TY;
+  v.box_x = K::BOX_X; v.box_y = K::BOX_Y;
+  v.halo_x = K::HALO_X; v.halo_y = K::HALO_Y;
   v.threads = G::THREADS; v.smem = G::SMEM_BYTES;
-  v.gap_dim = 1;
-  v.launch = &launch_rows<F, C, FMA>;
-  return v;
-}
-
-// rank-2 temporally blocked row marching (sweep_rows2.cuh)
-template <class F, class C, bool FMA> int launch_rows2(const SweepArgs &a) {
-  typedef Rows2Geom<F, C> G;
-  auto kernel = sweep_rows2<F, C, FMA>;
-  static int occ_cached[16] = {0};
-  int dev = 0;
-  cudaGetDevice(&dev);
-  if (dev < 0 || dev >= 16) dev = 0;
-  if (occ_cached[dev] == 0) {
-    cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, G::SMEM_BYTES);
-    if (e != cudaSuccess) return (int)e;
-    int occ = 0;
-    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kernel, G::THREADS, G::SMEM_BYTES);
-    if (e != cudaSuccess) return (int)e;
-    if (occ < 1) return (int)cudaErrorLaunchOutOfResources;
-    occ_cached[dev] = occ;
-  }
-  KParams<F> p;
-  fill_params<F>(p, a);
-  const int wy = a.whi[1] - a.wlo[1];
-  if (wy <= 0 || a.whi[2] <= a.wlo[2]) return 0;
-  p.cxo = a.wlo[2] / G::TX;
-  p.ncx = (a.whi[2] + G::TX - 1) / G::TX - p.cxo;
-  p.ncy = 1;
-  const int slots = a.sm_count * occ_cached[dev];
-  p.zchunk = a.zchunk > 0 ? std::min(a.zchunk, wy) : choose_zchunk(wy, p.ncx, slots, 2);
-  p.nchunks = (wy + p.zchunk - 1) / p.zchunk;
-  if (!set_gap(p, a, 1)) return (int)cudaErrorInvalidValue;
-  const long long items = (long long)p.nchunks * p.ncx;
-  if (items > 0x7fffffffLL) return (int)cudaErrorInvalidConfiguration;
-  p.nitems = (int)items;
-  const int grid = (int)std::min<long long>(items, slots);
-  kernel<<<grid, G::THREADS, G::SMEM_BYTES, a.stream>>>(p);
-  return (int)cudaGetLastError();
-}
-
-template <class F, class C, bool FMA> Variant rows2_variant(const char *name) {
-  typedef Rows2Geom<F, C> G;
-  Variant v;
-  v.name = name;
-  v.kind = VARIANT_TB2;
-  v.needs_tmap = false;
-  v.fma = FMA;
-  v.steps = 2;
-  v.tx = G::TX; v.ty = C::RB;
-  v.halo_x = 2 * G::VX; v.halo_y = 2;
-  v.threads = G::THREADS; v.smem = G::SMEM_BYTES;
-  v.gap_dim = 1;
-  v.launch = &launch_rows2<F, C, FMA>;
-  return v;
-}
-
-template <class F, class C, bool FMA, int MARCH = 0> Variant tb2_variant(const char *name) {
-  typedef typename Tb2GeomOf<F, C, MARCH>::type G;
-  Variant v;
-  v.name = name;
-  v.kind = VARIANT_TB2;
-  v.fma = FMA;
-  v.steps = 2;
-  v.tx = C::TX; v.ty = C::TY;
-  v.box_x = G::P0; v.box_y = G::BOX_Y;
-  v.halo_x = 2 * G::VX; v.halo_y = 2;
-  v.threads = G::THREADS; v.smem = G::SMEM_BYTES;
-  v.gap_dim = (MARCH <= 1 || MARCH == 4) ? 0 : -1;   // sweep_tb2, sweep_tb2m, sweep_tb2q
-  v.launch = &launch_tb2<F, C, FMA, MARCH>;
-  return v;
-}
-
-template <class F, class C, bool FMA> Variant tma_variant(const char *name) {
-  typedef TmaGeom<F, C> G;
-  Variant v;
-  v.name = name;
-  v.kind = VARIANT_TMA;
-  v.fma = FMA;
-  v.tx = C::TX; v.ty = C::TY;
-  v.box_x = G::SXP; v.box_y = G::SY;
-  v.halo_x = G::HX; v.halo_y = G::RY;
-  v.threads = G::THREADS; v.smem = G::SMEM_BYTES;
-  v.gap_dim = 0;
-  v.launch = &launch_tma<F, C, FMA>;
+  v.gap_dim = K::GAP_DIM;
+  v.launch = &launch_items<F, K>;
   return v;
 }
 
@@ -287,64 +173,44 @@ template <class F> struct BodyRegistrar {
     e.variants.push_back(d);
     d.fma = true; d.launch = &launch_direct<F, true>;
     e.variants.push_back(d);
-    // the staged kernel copies through the staged centre value, so it needs input 0 staged
+    // the staged kernel copies through the staged centre value, so it needs input 0 staged.
+    // One tile per kernel family and shape class: the r01 tile sweeps (profiles/r01_*) found these and nothing else
+    // ever won a comparison; the losers are gone from the binary (r01: 388 kernels, 38 MB).
     if constexpr (F::STAGED == 0 && F::RANK >= 2 && F::RZ <= 1 && F::RY <= 1 && F::RX <= 1) {
-      if constexpr (F::NIN > 4) {
-        e.variants.push_back(tma_variant<F, Tile3W, false>("tma:64x8"));
-        e.variants.push_back(tma_variant<F, Tile3W, true>("tma:64x8"));
-        if constexpr (F::RZ > 0) {
-          e.variants.push_back(tma_variant<F, Tile3W2, false>("tma:64x7"));
-          e.variants.push_back(tma_variant<F, Tile3W3, false>("tma:64x14"));
-        }
+      if constexpr (F::NIN > 4) {            // one coefficient field per tap (C4)
+        e.variants.push_back(item_variant<F, TmaK<F, Tile3W, false>, false>("tma:64x8"));
+        e.variants.push_back(item_variant<F, TmaK<F, Tile3W, true>, true>("tma:64x8"));
       } else if constexpr (F::RZ > 0) {
-        e.variants.push_back(tma_variant<F, Tile3A, false>("tma:64x16"));
-        e.variants.push_back(tma_variant<F, Tile3A, true>("tma:64x16"));
-        e.variants.push_back(tma_variant<F, Tile3B, false>("tma:128x8"));
-        e.variants.push_back(tma_variant<F, Tile3C, false>("tma:128x16"));
+        e.variants.push_back(item_variant<F, TmaK<F, Tile3A, false>, false>("tma:64x16"));
+        e.variants.push_back(item_variant<F, TmaK<F, Tile3A, true>, true>("tma:64x16"));
         if constexpr (F::NIN == 1 && F::RZ == 1) {
-          e.variants.push_back(tb2_variant<F, Tb2A, false>("tb2:64x16"));
-          e.variants.push_back(tb2_variant<F, Tb2A, true>("tb2:64x16"));
-          e.variants.push_back(tb2_variant<F, Tb2B, false>("tb2:64x16n7"));
-          e.variants.push_back(tb2_variant<F, Tb2C, false>("tb2:128x16"));
-          e.variants.push_back(tb2_variant<F, Tb2D, false>("tb2:64x32"));
+          e.variants.push_back(item_variant<F, Tb2K<F, Tb2A, false>, false>("tb2:64x16"));      // boxes narrower than 256
+          e.variants.push_back(item_variant<F, Tb2K<F, Tb2A, true>, true>("tb2:64x16"));
           if constexpr (F::ZSTAR) {
-            e.variants.push_back(tb2_variant<F, Tb2mA, false, 1>("tb2m:128x14"));
-            e.variants.push_back(tb2_variant<F, Tb2mA, true, 1>("tb2m:128x14"));
-            e.variants.push_back(tb2_variant<F, Tb2mB, false, 1>("tb2m:64x16"));
-            e.variants.push_back(tb2_variant<F, Tb2mC, false, 1>("tb2m:128x14n8"));
-            e.variants.push_back(tb2_variant<F, Tb2mD, false, 1>("tb2m:64x24"));
-            e.variants.push_back(tb2_variant<F, Tb2mA, false, 2>("tb2g:128x14"));
-            e.variants.push_back(tb2_variant<F, Tb2mD, false, 2>("tb2g:64x24"));
-            e.variants.push_back(tb2_variant<F, Tb2pA, false, 3>("tb2p:128x14"));
-            e.variants.push_back(tb2_variant<F, Tb2pB, false, 3>("tb2p:64x24"));
-            e.variants.push_back(tb2_variant<F, Tb2pA, true, 3>("tb2p:128x14"));
-            e.variants.push_back(tb2_variant<F, Tb2pA, false, 4>("tb2q:128x14"));
-            e.variants.push_back(tb2_variant<F, Tb2pA, true, 4>("tb2q:128x14"));
+            e.variants.push_back(item_variant<F, Tb2mK<F, Tb2mA, false>, false>("tb2m:128x14"));   // thin launches (slab boundary planes)
+            e.variants.push_back(item_variant<F, Tb2mK<F, Tb2mA, true>, true>("tb2m:128x14"));
+            e.variants.push_back(item_variant<F, Tb2qK<F, Tb2pA, false>, false>("tb2q:128x14"));   // the default on wide, deep boxes (C3)
+            e.variants.push_back(item_variant<F, Tb2qK<F, Tb2pA, true>, true>("tb2q:128x14"));
           }
         } else if constexpr (F::NIN == 2 && F::RZ == 1 && F::ZSTAR) {
-          // input 0 plus pointwise inputs (Jacobi with a right-hand side): the z-marching form only
-          e.variants.push_back(tb2_variant<F, Tb2mG, false, 1>("tb2m:64x24"));
-          e.variants.push_back(tb2_variant<F, Tb2mG, true, 1>("tb2m:64x24"));
-          e.variants.push_back(tb2_variant<F, Tb2mE, false, 1>("tb2m:128x10"));
-          e.variants.push_back(tb2_variant<F, Tb2mF, false, 1>("tb2m:128x14"));
+          // input 0 plus a pointwise input (Jacobi with a right-hand side, C5): the z-marching form only
+          e.variants.push_back(item_variant<F, Tb2mK<F, Tb2mG, false>, false>("tb2m:64x24"));
+          e.variants.push_back(item_variant<F, Tb2mK<F, Tb2mG, true>, true>("tb2m:64x24"));
+          e.variants.push_back(item_variant<F, Tb2mK<F, Tb2mF, false>, false>("tb2m:128x14"));
         }
       } else {
         if constexpr (F::RANK == 2 && F::RY == 1 && F::NIN <= 4) {
-          e.variants.push_back(rows_variant<F, Rows512, false>("rows:512"));
-          e.variants.push_back(rows_variant<F, Rows512, true>("rows:512"));
-          e.variants.push_back(rows_variant<F, Rows256, false>("rows:256"));
-          e.variants.push_back(rows_variant<F, Rows1024, false>("rows:1024"));
+          e.variants.push_back(item_variant<F, RowsK<F, Rows512, false>, false>("rows:512"));
+          e.variants.push_back(item_variant<F, RowsK<F, Rows512, true>, true>("rows:512"));
+          e.variants.push_back(item_variant<F, RowsK<F, Rows256, false>, false>("rows:256"));
+          e.variants.push_back(item_variant<F, RowsK<F, Rows1024, false>, false>("rows:1024"));
           if constexpr (F::NIN == 1) {
-            e.variants.push_back(rows2_variant<F, Rows2A, false>("tb2r:256x3"));
-            e.variants.push_back(rows2_variant<F, Rows2A, true>("tb2r:256x3"));
-            e.variants.push_back(rows2_variant<F, Rows2B, false>("tb2r:256x6"));
-            e.variants.push_back(rows2_variant<F, Rows2C, false>("tb2r:512x3"));
+            e.variants.push_back(item_variant<F, Rows2K<F, Rows2A, false>, false>("tb2r:256x3"));
+            e.variants.push_back(item_variant<F, Rows2K<F, Rows2A, true>, true>("tb2r:256x3"));
           }
         }
-        e.variants.push_back(tma_variant<F, Tile2A, false>("tma:128x32"));
-        e.variants.push_back(tma_variant<F, Tile2A, true>("tma:128x32"));
-        e.variants.push_back(tma_variant<F, Tile2B, false>("tma:128x16"));
-        e.variants.push_back(tma_variant<F, Tile2C, false>("tma:64x64"));
+        e.variants.push_back(item_variant<F, TmaK<F, Tile2A, false>, false>("tma:128x32"));
+        e.variants.push_back(item_variant<F, TmaK<F, Tile2A, true>, true>("tma:128x32"));
       }
     }
     register_body(std::move(e));

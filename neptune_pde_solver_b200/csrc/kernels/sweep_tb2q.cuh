@@ -1,25 +1,44 @@
-// Temporally blocked z-march, lean steady state (sm_100a): sweep_tb2p's data movement with a steady-state
-// group that carries no per-point bookkeeping.
+// Temporally blocked z-march, grouped and software-pipelined, with a lean steady state (sm_100a).  The default
+// kernel of `neptune_rt_run_steps` on wide, deep single-input 3-D boxes (BASELINE configs[2]).
+//
+// Data movement (r01's sweep_tb2p, which this kernel replaces): geometry, TMA producer and z-star register windows of
+// sweep_tb2m.cuh, but three planes per consumer barrier, and phase B of the PREVIOUS group riding in the same steps
+// as phase A of the current one.  Step R of a group:
+//     A : level-0 plane k arrives  -> level-1 plane k-1 (stored to the level-1 ring)
+//     B': level-2 plane k-LAG        <- level-1 planes k-6, k-5, k-4 (all produced before the last barrier)
+// so both levels' fp64 chains interleave in one instruction stream, with ONE consumer barrier per three planes.  The
+// level-1 ring holds seven planes (three being written, four being read); an item runs three extra steps to drain.
 //
 // r01 ncu of sweep_tb2p on C3 (profiles/r01_c3_tb2p_128x14_ncu.txt): 42.5 thread instructions per point-update
-// against 9 fp64 operations; the steady loop is 832 SASS instructions per three planes of which 216 are DADD/DMUL,
+// against 9 fp64 operations; the steady loop was 832 SASS instructions per three planes of which 216 DADD/DMUL,
 // 96 FSEL (copy-through selects), 32 SEL, 45 ISETP, 22 BRA, ~250 IMAD/VIADD/LOP3/LEA/R2UR/LDC (masks, slot
-// addresses, window rotation moves).  Here
+// addresses, window rotation moves, shared-window base rebuilt from SR_CgaCtaId under register pressure).  Here
 //   * the z windows of both levels live in THREE statically indexed register blocks, slot (step + q) mod 3, so a
 //     group of three planes ends where it began and no register is moved;
 //   * a group whose three steps are all in steady state AND whose planes all lie inside the apply's z bounds takes
 //     the lean path: both levels are evaluated unconditionally in one basic block (eight independent fp64 chains
 //     per thread), then ONE branch that only threads with a point outside the y/x bounds take applies the
-//     copy-through selects, then the stores go out under per-item row predicates;
-//   * every other group (pipeline fill and drain, the first and last planes of the box) runs the fully masked
-//     step of sweep_tb2p.
+//     copy-through selects, then the stores go out;
+//   * shared memory is addressed by 32-bit shared-window addresses + immediate offsets (inline PTX), thread-constant
+//     values are made opaque to the compiler so that they stay in registers instead of being recomputed per plane;
+//   * row pitches are padded so that warps straddling two thread rows do not bank-conflict (Tb2qGeom);
+//   * warps made of ring threads only run a copy of the loop without phase B';
+//   * every other group (pipeline fill and drain, the first and last planes of the box) runs the fully masked step.
 // Ring threads evaluate level 2 as well (its loads stay inside the guarded rings) and simply store nothing: a
 // warp instruction costs the same with or without them, and the branch that used to skip them split the stream.
 // Arithmetic is the body functor at both levels: bit-identical to two single sweeps.
+// r02, C3 512^3 f64: 584 Gupd/s (sweep_tb2p: 466-476), 31.4 -> 29 thread instructions per update, shared wavefronts
+// 95.9 M -> 80.2 M per launch (profiles/r02_c3_tb2q_ncu.txt).
 #pragma once
-#include "sweep_tb2p.cuh"
+#include "sweep_tb2m.cuh"
 
 namespace neptune {
+
+// GS = planes per barrier group.  Level-1 ring = 2*GS + 1 planes (GS being written, GS + 1 being read); phase B' lags
+// phase A by GS + 1 planes.  GS = 3 needs no register rotation with three-slot z windows.
+template <int TX_, int TY_, int VY_, int NS_, int MINB_, int GS_ = 3> struct Tb2pCfg : Tb2Cfg<TX_, TY_, VY_, NS_, MINB_> {
+  static constexpr int GS = GS_;
+};
 
 
 // Shared-memory access by 32-bit shared-window address + immediate byte offset.  Generic pointers into dynamic
@@ -159,15 +178,8 @@ sweep_tb2q(const __grid_constant__ KParams<F> p, const __grid_constant__ CUtenso
         int zb, ze, y0, x0;
         geom(item, zb, ze, y0, x0);
         const int nslots = ze - zb + 4;
-        // the ring holds NS = 4 planes, about two plane-steps of look-ahead (r02 ncu: the consumers still waited on the
-        // full barriers, long_scoreboard 1.47 per issue).  Shared memory has no room for more stages, L2 has: the
-        // producer asks the TMA unit to PREFETCH plane j + PF into L2 when it loads plane j, so the load proper is an
-        // L2 hit.
-        constexpr int PF = C::NS + 4;
-        for (int j = 0; j < min(PF, nslots); ++j) tma_prefetch_3d(&tmap, x0 - 2 * VX, y0 - 2, zb - 2 + j);
         for (int j = 0; j < nslots; ++j, ++n) {
           const unsigned s = n % NS;
-          if (j + PF < nslots) tma_prefetch_3d(&tmap, x0 - 2 * VX, y0 - 2, zb - 2 + j + PF);
           mbar_wait(empty0 + 8 * s, ((n / NS) & 1) ^ 1);
           mbar_expect_tx(full0 + 8 * s, G::STAGE_TX_BYTES);
           tma_load_3d(stage0 + s * G::SLOT_BYTES, &tmap, x0 - 2 * VX, y0 - 2, zb - 2 + j, full0 + 8 * s);
@@ -256,7 +268,9 @@ sweep_tb2q(const __grid_constant__ KParams<F> p, const __grid_constant__ CUtenso
           s_prv = s;
           prv = cur;
           if (++s == NS) { s = 0; ph ^= 1; }
-          // level-1 reads of phase B' (planes produced before the last barrier)
+          // level-1 reads of phase B' (planes produced before the last barrier).  They come AFTER the level-0 reads in
+          // program order: issued ahead of the wait for the level-0 plane (they do not depend on it) they stay live
+          // across it, and at 96 registers that spills (r02: 429 instead of 584 Gupd/s on C3)
           if constexpr (WITH_B) {
             const uint32_t pnew = t1 + slot(c1, GS + 1) * (uint32_t)G::L1_BYTES;   // plane k-LAG+1
             const uint32_t pctr = t1 + slot(c1, GS) * (uint32_t)G::L1_BYTES;       // plane k-LAG

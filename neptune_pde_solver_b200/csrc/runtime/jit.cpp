@@ -226,8 +226,7 @@ bool read_file(const std::string &path, std::string &out) {
 }
 
 uint64_t header_digest(const std::string &csrc) {
-  static const char *files[] = {"common.cuh", "tiles.cuh", "sweep_direct.cuh", "sweep_tma.cuh", "sweep_tb2.cuh", "sweep_tb2m.cuh", "sweep_tb2g.cuh",
-                                "sweep_tb2p.cuh", "sweep_tb2q.cuh", "sweep_rows.cuh", "sweep_rows2.cuh"};
+  static const char *files[] = {"common.cuh", "tiles.cuh", "sweep_direct.cuh", "sweep_tma.cuh", "sweep_tb2.cuh", "sweep_tb2m.cuh", "sweep_tb2q.cuh", "sweep_rows.cuh", "sweep_rows2.cuh"};
   uint64_t h = 1469598103934665603ull;
   for (const char *f : files) {
     std::string s;

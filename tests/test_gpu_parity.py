@@ -412,12 +412,11 @@ def test_temporal_blocking_bit_exact(nb, ctx, name, shape, ty, steps):
     try:
         st = m.stencil(ctx, 0)
         ran = []
-        for tbv in ["tb2:64x16", "tb2:64x16n7", "tb2:128x16", "tb2:64x32", "tb2m:128x14", "tb2m:64x16", "tb2m:128x14n8", "tb2m:64x24",
-                    "tb2g:128x14", "tb2g:64x24", "tb2p:128x14", "tb2p:64x24", "tb2q:128x14"]:
+        for tbv in ["tb2:64x16", "tb2m:128x14", "tb2q:128x14"]:
             try:
                 st.set("variant", tbv)
             except nb.NeptuneError:
-                assert tbv.startswith(("tb2m:", "tb2g:", "tb2p:", "tb2q:")) and name == "weighted_3d27"   # z-marching needs centre-column z taps
+                assert tbv.startswith(("tb2m:", "tb2q:")) and name == "weighted_3d27"   # z-marching needs centre-column z taps
                 continue
             ran.append(tbv)
             fa, fb = nb.Field.from_numpy(ctx, u), nb.Field.from_numpy(ctx, u)
@@ -429,7 +428,7 @@ def test_temporal_blocking_bit_exact(nb, ctx, name, shape, ty, steps):
             if steps >= 2 and steps % 2 == 0:
                 assert st.variant() == tbv
             fa.free(); fb.free()
-        assert len(ran) >= (4 if name == "weighted_3d27" else 8)
+        assert len(ran) >= (1 if name == "weighted_3d27" else 3)
         st.set("tblock", 1)
         fa, fb = nb.Field.from_numpy(ctx, u), nb.Field.from_numpy(ctx, u)
         n0 = ctx.launch_count()
@@ -459,7 +458,7 @@ def test_temporal_blocking_2d_bit_exact(nb, ctx, name, shape, ty, steps):
     m = nb.Module(text)
     try:
         st = m.stencil(ctx, 0)
-        for tbv in ["auto", "tb2r:256x3", "tb2r:256x6", "tb2r:512x3"]:
+        for tbv in ["auto", "tb2r:256x3"]:
             for zc in ("0", "16", "7"):
                 if tbv != "auto":
                     st.set("variant", tbv)
@@ -513,7 +512,7 @@ def test_temporal_blocking_with_a_pointwise_input(nb, ctx, shape, ty, steps):
     m = nb.Module(text)
     try:
         st = m.stencil(ctx, 0)
-        for tbv in ["auto", "tb2m:64x24", "tb2m:128x10", "tb2m:128x14"]:
+        for tbv in ["auto", "tb2m:64x24", "tb2m:128x14"]:
             if tbv != "auto":
                 st.set("variant", tbv)
             fa, fb = nb.Field.from_numpy(ctx, u), nb.Field.from_numpy(ctx, u)
@@ -808,8 +807,8 @@ def test_matrix_free_operator_on_caller_owned_device_vectors(nb, ctx):
 
 
 @pytest.mark.parametrize("name,shape,variants", [
-    ("heat_star", (96, 112, 256), ["tb2:128x16", "tb2m:128x14", "tb2g:128x14", "tb2m:64x24", "tb2p:128x14", "tb2p:64x24", "tb2q:128x14"]),
-    ("heat_box_2d9", (1536, 2032), ["tb2r:256x3", "tb2r:512x3"]),
+    ("heat_star", (96, 112, 256), ["tb2:64x16", "tb2m:128x14", "tb2q:128x14"]),
+    ("heat_box_2d9", (1536, 2032), ["tb2r:256x3"]),
     ("jacobi_star", (96, 96, 192), ["tb2m:64x24", "tb2m:128x14"]),
 ])
 def test_temporally_blocked_kernels_repeat_bitwise(nb, ctx, name, shape, variants):
