@@ -632,9 +632,12 @@ def run_b200(args):
             "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": ty, "data": "synthetic",
             "config": {"workload": descr, "grid_per_gpu": list(shape1), "global_grid": gshape,
-                       "decomposition": ("dim-0 slabs, %d ghost plane(s) per neighbour side, %d step(s) per launch, one NCCL send/recv exchange of %d plane(s) every %d step(s), "
-                                         "overlapped with the interior sweep of the launch that precedes it"
-                                         % (slab.halo, 2 if variant.startswith("tb2") else 1, slab.halo, max(1, slab.halo // max(1, gdesc.radius0())))) if world > 1 else "single domain",
+                       "decomposition": ("dim-0 slabs, %d ghost plane(s) per neighbour side, %d step(s) per launch, one exchange of %d plane(s) every %d step(s) "
+                                         "(%s), overlapped with the interior sweep of the launch that produces them"
+                                         % (slab.halo, 2 if variant.startswith("tb2") else 1, slab.halo, max(1, slab.halo // max(1, gdesc.radius0())),
+                                            {"p2p": "pushed into the neighbour's field by a copy engine over NVLink, CUDA IPC + stream memory-op flags",
+                                             "nccl": "ncclSend/ncclRecv"}.get(stencil.halo_mode(), "?"))) if world > 1 else "single domain",
+                       "halo_mode": stencil.halo_mode() if world > 1 else None,
                        "points_per_step": int(total_points), "kernel_variant": variant,
                        "timing": "median of %d repetitions of exactly %d steps each, CUDA events on the sweep stream, max over ranks per repetition" % (len(rep_ms), args.steps),
                        "rep_ms": [round(x, 4) for x in rep_ms], "rep_spread": (max(rep_ms) - min(rep_ms)) / ms if ms > 0 else None,

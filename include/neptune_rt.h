@@ -224,6 +224,14 @@ int neptune_rt_slab_localize(const neptune_rt_stencil_desc *global_desc, int nra
  * alignment) are agreed by all ranks with one small ncclAllReduce per (fields, settings). */
 int neptune_rt_stencil_set_slab(neptune_rt_stencil *stencil, int64_t ghost, int64_t global_lb0,
                                 int64_t global_ub0);
+/* How the last slab-mode neptune_rt_run_steps of this stencil exchanged ghost planes ("" before the first):
+ *   "p2p"  — the default between GPUs of one node: every rank PUSHES its boundary planes into the neighbour's field
+ *            memory (CUDA IPC mapping) with a copy engine over NVLink, ordered by stream memory operations
+ *            (cuStreamWriteValue32 / cuStreamWaitValue32) on four flag words per rank; no kernel, hence no SM, takes part,
+ *            so the exchange really runs beside the persistent interior launch (which holds every SM's shared memory);
+ *   "nccl" — ncclSend/ncclRecv groups on the high-priority stream: NEPTUNE_RT_HALO=nccl, caller-owned (wrapped) field
+ *            memory, or when IPC / stream memory operations are unavailable. All ranks agree on one mode. */
+const char *neptune_rt_stencil_halo_mode(neptune_rt_stencil *stencil);
 /* 128-byte NCCL unique id (rank 0 creates it; the host harness broadcasts it). */
 int neptune_rt_comm_unique_id(void *id128);
 int neptune_rt_comm_init(neptune_rt_ctx *ctx, const void *id128, int nranks, int rank);

@@ -182,7 +182,9 @@ sweep_tma(const __grid_constant__ KParams<F> p, const __grid_constant__ CUtensor
   constexpr bool LATE_PW = F::NIN > 4;
 
   extern __shared__ __align__(128) unsigned char smem_raw[];
-  unsigned char *smem = reinterpret_cast<unsigned char *>((reinterpret_cast<uintptr_t>(smem_raw) + 127) & ~uintptr_t(127));
+  // (pointer arithmetic, not a round trip through an integer: the latter loses the shared address space and every
+  // window read became a generic LD.E instead of LDS — r02 SASS census)
+  unsigned char *smem = smem_raw + ((128u - (smem_u32(smem_raw) & 127u)) & 127u);
   const uint32_t full0 = smem_u32(smem + NS * G::STAGE_BYTES);  // full[s]: TMA bytes of stage s have landed
   const uint32_t empty0 = full0 + 8 * NS;                       // empty[s]: every consumer warp is done with stage s
   const uint32_t stage0 = smem_u32(smem);

@@ -125,6 +125,16 @@ struct neptune_rt_ctx {
   int trace_groups = 0;
   std::vector<int> trace_kind;             // per group: steps advanced * 10 + (1 = exchanged)
   std::vector<std::function<void()>> on_finalize;
+  // peer-to-peer halo path (same node): ghost planes are PUSHED into the neighbour's field memory by a copy engine over
+  // NVLink (cudaMemcpyAsync into CUDA-IPC-mapped memory) and ordered with stream memory operations on four flag words
+  // per rank, so that no kernel — and therefore no SM — takes part in the exchange
+  bool p2p = false;
+  uint32_t *flags = nullptr;                       // [0] READY from up, [1] READY from down, [2] ARRIVED from up, [3] ARRIVED from down
+  uint32_t *peer_flags[2] = {nullptr, nullptr};    // the up / down neighbour's flag words (IPC-mapped)
+  uint32_t epoch = 0;                              // exchanges so far (the same on every rank: SPMD)
+  unsigned wait_flags = 0;
+  CUresult (*StreamWriteValue32)(CUstream, CUdeviceptr, cuuint32_t, unsigned) = nullptr;
+  CUresult (*StreamWaitValue32)(CUstream, CUdeviceptr, cuuint32_t, unsigned) = nullptr;
 };
 
 struct neptune_rt_field {
@@ -135,6 +145,10 @@ struct neptune_rt_field {
   void *dptr = nullptr;
   size_t bytes = 0;
   bool owned = true;   // false: caller's device memory (neptune_rt_field_wrap_device)
+  // peer-to-peer halo path: the up / down neighbour's corresponding field, IPC-mapped, and where my boundary planes land in it
+  bool peer_mapped = false;
+  void *peer_base[2] = {nullptr, nullptr};
+  size_t peer_off[2] = {0, 0};
   size_t elsize() const { return dtype == NEPTUNE_RT_F64 ? 8 : 4; }
   int64_t numel() const { return ext[0] * ext[1] * ext[2]; }
 };
@@ -165,7 +179,7 @@ struct neptune_rt_stencil {
   bool slab_loop = false;   // set by neptune_rt_run_steps around its slab launches: dim-0 bounds are the GLOBAL ones
   // what the ranks agreed for the last (fields, settings) neptune_rt_run_steps saw in slab mode
   struct Agreed {
-    bool valid = false, fuse2 = false, split = false;
+    bool valid = false, fuse2 = false, split = false, p2p = false;
     neptune_rt_field *a = nullptr, *b = nullptr;
     std::vector<neptune_rt_field *> extra;
     int tblock = 0;
@@ -371,6 +385,9 @@ extern "C" int neptune_rt_finalize(neptune_rt_ctx *c) {
   for (cudaEvent_t e : c->trace_events) cudaEventDestroy(e);
   if (c->red_partials) cudaFree(c->red_partials);
   if (c->red_host) cudaFreeHost(c->red_host);
+  for (uint32_t *pf : c->peer_flags)
+    if (pf) cudaIpcCloseMemHandle(pf);
+  if (c->flags) cudaFree(c->flags);
   if (c->agree_dev) cudaFree(c->agree_dev);
   if (c->agree_host) cudaFreeHost(c->agree_host);
   for (auto &fn : c->on_finalize) fn();
@@ -427,6 +444,8 @@ extern "C" int neptune_rt_field_free(neptune_rt_field *f) {
   // the halo, upload and download streams may still be reading or writing this field
   for (cudaStream_t st : {f->ctx->halo_stream, f->ctx->h2d_stream, f->ctx->stream, f->ctx->d2h_stream})
     if (st) cudaStreamSynchronize(st);
+  for (void *pb : f->peer_base)
+    if (pb) cudaIpcCloseMemHandle(pb);
   if (f->owned) cudaFree(f->dptr);
   delete f;
   return NEPTUNE_RT_OK;
@@ -1082,6 +1101,10 @@ extern "C" int neptune_rt_slab_localize(const neptune_rt_stencil_desc *g, int nr
   return NEPTUNE_RT_OK;
 }
 
+namespace {
+void p2p_setup(neptune_rt_ctx *c);   // below, with the rest of the peer-to-peer halo path
+}
+
 extern "C" int neptune_rt_comm_unique_id(void *id128) {
   if (!id128) return set_error(nullptr, NEPTUNE_RT_EINVAL, "comm_unique_id: NULL");
   if (!nccl().ok) return set_error(nullptr, NEPTUNE_RT_ENCCL, "NCCL (libnccl.so.2) could not be loaded");
@@ -1119,9 +1142,163 @@ extern "C" int neptune_rt_comm_init(neptune_rt_ctx *c, const void *id128, int nr
     RT_NCCL(c, nccl().GroupEnd());
     RT_CUDA(c, cudaStreamSynchronize(c->halo_stream));
     RT_CUDA(c, cudaFree(buf));
+    p2p_setup(c);
   }
   return NEPTUNE_RT_OK;
 }
+
+namespace {
+
+// `n` bytes to and from each dim-0 neighbour (set-up traffic: IPC handles), through NCCL; synchronous
+int neighbour_swap(neptune_rt_ctx *c, const void *to_up, void *from_up, const void *to_down, void *from_down, size_t n) {
+  const bool up = c->rank > 0, down = c->rank + 1 < c->nranks;
+  char *buf = nullptr;
+  RT_CUDA(c, cudaMalloc(&buf, 4 * n));
+  if (up) RT_CUDA(c, cudaMemcpyAsync(buf, to_up, n, cudaMemcpyHostToDevice, c->halo_stream));
+  if (down) RT_CUDA(c, cudaMemcpyAsync(buf + 2 * n, to_down, n, cudaMemcpyHostToDevice, c->halo_stream));
+  RT_NCCL(c, nccl().GroupStart());
+  if (up) {
+    RT_NCCL(c, nccl().Send(buf, n, ncclChar, c->rank - 1, c->comm, c->halo_stream));
+    RT_NCCL(c, nccl().Recv(buf + n, n, ncclChar, c->rank - 1, c->comm, c->halo_stream));
+  }
+  if (down) {
+    RT_NCCL(c, nccl().Send(buf + 2 * n, n, ncclChar, c->rank + 1, c->comm, c->halo_stream));
+    RT_NCCL(c, nccl().Recv(buf + 3 * n, n, ncclChar, c->rank + 1, c->comm, c->halo_stream));
+  }
+  RT_NCCL(c, nccl().GroupEnd());
+  if (up) RT_CUDA(c, cudaMemcpyAsync(from_up, buf + n, n, cudaMemcpyDeviceToHost, c->halo_stream));
+  if (down) RT_CUDA(c, cudaMemcpyAsync(from_down, buf + 3 * n, n, cudaMemcpyDeviceToHost, c->halo_stream));
+  RT_CUDA(c, cudaStreamSynchronize(c->halo_stream));
+  RT_CUDA(c, cudaFree(buf));
+  return NEPTUNE_RT_OK;
+}
+
+// flag words + the neighbours' flag words; any failure leaves c->p2p false (the NCCL exchange is then used; the ranks
+// agree on the mode in neptune_rt_run_steps)
+void p2p_setup(neptune_rt_ctx *c) {
+  const char *mode = std::getenv("NEPTUNE_RT_HALO");
+  if (mode && std::strcmp(mode, "nccl") == 0) return;
+  auto get = [](const char *name) -> void * {
+    void *p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint(name, &p, cudaEnableDefault, &q) != cudaSuccess || q != cudaDriverEntryPointSuccess) return nullptr;
+    return p;
+  };
+  c->StreamWriteValue32 = reinterpret_cast<decltype(c->StreamWriteValue32)>(get("cuStreamWriteValue32"));
+  c->StreamWaitValue32 = reinterpret_cast<decltype(c->StreamWaitValue32)>(get("cuStreamWaitValue32"));
+  if (!c->StreamWriteValue32 || !c->StreamWaitValue32) return;
+  if (cudaMalloc(&c->flags, 64) != cudaSuccess) { c->flags = nullptr; cudaGetLastError(); return; }
+  cudaMemset(c->flags, 0, 64);
+  cudaDeviceSynchronize();
+  // self-test of the stream memory operations, with the remote-write flush where the device has it
+  c->wait_flags = CU_STREAM_WAIT_VALUE_GEQ | CU_STREAM_WAIT_VALUE_FLUSH;
+  bool ok = c->StreamWriteValue32((CUstream)c->halo_stream, (CUdeviceptr)(c->flags + 8), 1u, CU_STREAM_WRITE_VALUE_DEFAULT) == CUDA_SUCCESS;
+  if (ok && c->StreamWaitValue32((CUstream)c->halo_stream, (CUdeviceptr)(c->flags + 8), 1u, c->wait_flags) != CUDA_SUCCESS) {
+    c->wait_flags = CU_STREAM_WAIT_VALUE_GEQ;
+    ok = c->StreamWaitValue32((CUstream)c->halo_stream, (CUdeviceptr)(c->flags + 8), 1u, c->wait_flags) == CUDA_SUCCESS;
+  }
+  ok = ok && cudaStreamSynchronize(c->halo_stream) == cudaSuccess;
+  cudaIpcMemHandle_t mine, from_up, from_down;
+  std::memset(&from_up, 0, sizeof from_up);
+  std::memset(&from_down, 0, sizeof from_down);
+  ok = ok && cudaIpcGetMemHandle(&mine, c->flags) == cudaSuccess;
+  if (!ok) std::memset(&mine, 0, sizeof mine);      // still take part in the swap: the neighbours are waiting for it
+  char tx[128] = {0}, rx_up[128] = {0}, rx_down[128] = {0};
+  tx[0] = ok ? 1 : 0;
+  std::memcpy(tx + 8, &mine, sizeof mine);
+  if (neighbour_swap(c, tx, rx_up, tx, rx_down, sizeof tx) != NEPTUNE_RT_OK) { cudaGetLastError(); return; }
+  const bool up = c->rank > 0, down = c->rank + 1 < c->nranks;
+  if (up) {
+    std::memcpy(&from_up, rx_up + 8, sizeof from_up);
+    ok = ok && rx_up[0] == 1 && cudaIpcOpenMemHandle((void **)&c->peer_flags[0], from_up, cudaIpcMemLazyEnablePeerAccess) == cudaSuccess;
+  }
+  if (down) {
+    std::memcpy(&from_down, rx_down + 8, sizeof from_down);
+    ok = ok && rx_down[0] == 1 && cudaIpcOpenMemHandle((void **)&c->peer_flags[1], from_down, cudaIpcMemLazyEnablePeerAccess) == cudaSuccess;
+  }
+  cudaGetLastError();
+  c->p2p = ok;
+}
+
+// the neighbours' copies of `f`, mapped into this process, and where this rank's boundary planes land in them
+int p2p_map_field(neptune_rt_ctx *c, neptune_rt_field *f, int64_t own_b, int64_t own_e, int64_t ghost, bool *ok_out) {
+  const int cd0 = 3 - f->rank;
+  const size_t plane = f->ext[cd0] ? f->bytes / (size_t)f->ext[cd0] : 0;
+  bool ok = f->owned;                               // wrapped memory may sit inside another allocation: not exportable as it is
+  cudaIpcMemHandle_t mine;
+  std::memset(&mine, 0, sizeof mine);
+  ok = ok && cudaIpcGetMemHandle(&mine, f->dptr) == cudaSuccess;
+  cudaGetLastError();
+  // to the up neighbour: "your last owned planes go to my rows [own_b - ghost, own_b)"; to the down one: "... [own_e, own_e + ghost)"
+  char tx_up[128] = {0}, tx_down[128] = {0}, rx_up[128] = {0}, rx_down[128] = {0};
+  const uint64_t off_from_up = (uint64_t)(own_b - ghost) * plane, off_from_down = (uint64_t)own_e * plane;
+  tx_up[0] = tx_down[0] = ok ? 1 : 0;
+  std::memcpy(tx_up + 8, &mine, sizeof mine);   std::memcpy(tx_up + 8 + sizeof mine, &off_from_up, 8);
+  std::memcpy(tx_down + 8, &mine, sizeof mine); std::memcpy(tx_down + 8 + sizeof mine, &off_from_down, 8);
+  if (int rc = neighbour_swap(c, tx_up, rx_up, tx_down, rx_down, 128)) return rc;
+  const bool up = c->rank > 0, down = c->rank + 1 < c->nranks;
+  for (int side = 0; side < 2; ++side) {
+    if (!(side == 0 ? up : down)) continue;
+    const char *rx = side == 0 ? rx_up : rx_down;
+    cudaIpcMemHandle_t h;
+    std::memcpy(&h, rx + 8, sizeof h);
+    uint64_t off = 0;
+    std::memcpy(&off, rx + 8 + sizeof h, 8);
+    if (ok && rx[0] == 1 && !f->peer_base[side]) {
+      if (cudaIpcOpenMemHandle(&f->peer_base[side], h, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) { f->peer_base[side] = nullptr; ok = false; cudaGetLastError(); }
+    } else if (rx[0] != 1) {
+      ok = false;
+    }
+    f->peer_off[side] = (size_t)off;
+  }
+  f->peer_mapped = ok;
+  *ok_out = ok;
+  return NEPTUNE_RT_OK;
+}
+
+// One exchange of `w` = ghost planes of `f` in p2p mode, in three parts:
+//   announce (sweep stream, after the last launch of this rank that touches f's ghost planes): tell the neighbours that
+//            they may overwrite my ghost planes;
+//   push     (halo stream, after the boundary planes are computed): wait for the neighbour's announcement, copy my
+//            boundary planes into its ghost planes, tell it they have arrived;
+//   join     (sweep stream, before the next launch that reads ghost planes): wait for both neighbours' data.
+int p2p_announce(neptune_rt_ctx *c, uint32_t e) {
+  const bool up = c->rank > 0, down = c->rank + 1 < c->nranks;
+  // I am the up neighbour's DOWN neighbour: its word [1]; and the down neighbour's UP neighbour: its word [0]
+  if (up && c->StreamWriteValue32((CUstream)c->stream, (CUdeviceptr)(c->peer_flags[0] + 1), e, CU_STREAM_WRITE_VALUE_DEFAULT) != CUDA_SUCCESS)
+    return set_error(c, NEPTUNE_RT_ECUDA, "cuStreamWriteValue32 (halo announce) failed");
+  if (down && c->StreamWriteValue32((CUstream)c->stream, (CUdeviceptr)(c->peer_flags[1] + 0), e, CU_STREAM_WRITE_VALUE_DEFAULT) != CUDA_SUCCESS)
+    return set_error(c, NEPTUNE_RT_ECUDA, "cuStreamWriteValue32 (halo announce) failed");
+  return NEPTUNE_RT_OK;
+}
+int p2p_push(neptune_rt_ctx *c, neptune_rt_field *f, int64_t own_b, int64_t own_e, int64_t w, uint32_t e) {
+  const bool up = c->rank > 0, down = c->rank + 1 < c->nranks;
+  const int cd0 = 3 - f->rank;
+  const size_t plane = f->ext[cd0] ? f->bytes / (size_t)f->ext[cd0] : 0, n = plane * (size_t)w;
+  char *base = (char *)f->dptr;
+  CUstream H = (CUstream)c->halo_stream;
+  if (up) {
+    if (c->StreamWaitValue32(H, (CUdeviceptr)(c->flags + 0), e, c->wait_flags) != CUDA_SUCCESS) return set_error(c, NEPTUNE_RT_ECUDA, "cuStreamWaitValue32 (halo push) failed");
+    RT_CUDA(c, cudaMemcpyAsync((char *)f->peer_base[0] + f->peer_off[0], base + (size_t)own_b * plane, n, cudaMemcpyDeviceToDevice, c->halo_stream));
+    if (c->StreamWriteValue32(H, (CUdeviceptr)(c->peer_flags[0] + 3), e, CU_STREAM_WRITE_VALUE_DEFAULT) != CUDA_SUCCESS) return set_error(c, NEPTUNE_RT_ECUDA, "cuStreamWriteValue32 (halo arrived) failed");
+  }
+  if (down) {
+    if (c->StreamWaitValue32(H, (CUdeviceptr)(c->flags + 1), e, c->wait_flags) != CUDA_SUCCESS) return set_error(c, NEPTUNE_RT_ECUDA, "cuStreamWaitValue32 (halo push) failed");
+    RT_CUDA(c, cudaMemcpyAsync((char *)f->peer_base[1] + f->peer_off[1], base + (size_t)(own_e - w) * plane, n, cudaMemcpyDeviceToDevice, c->halo_stream));
+    if (c->StreamWriteValue32(H, (CUdeviceptr)(c->peer_flags[1] + 2), e, CU_STREAM_WRITE_VALUE_DEFAULT) != CUDA_SUCCESS) return set_error(c, NEPTUNE_RT_ECUDA, "cuStreamWriteValue32 (halo arrived) failed");
+  }
+  return NEPTUNE_RT_OK;
+}
+int p2p_join(neptune_rt_ctx *c, uint32_t e) {
+  const bool up = c->rank > 0, down = c->rank + 1 < c->nranks;
+  if (up && c->StreamWaitValue32((CUstream)c->stream, (CUdeviceptr)(c->flags + 2), e, c->wait_flags) != CUDA_SUCCESS)
+    return set_error(c, NEPTUNE_RT_ECUDA, "cuStreamWaitValue32 (halo join) failed");
+  if (down && c->StreamWaitValue32((CUstream)c->stream, (CUdeviceptr)(c->flags + 3), e, c->wait_flags) != CUDA_SUCCESS)
+    return set_error(c, NEPTUNE_RT_ECUDA, "cuStreamWaitValue32 (halo join) failed");
+  return NEPTUNE_RT_OK;
+}
+
+}  // namespace
 
 extern "C" int neptune_rt_halo_exchange(neptune_rt_ctx *c, neptune_rt_field *f, int64_t own_begin, int64_t own_end,
                                         int64_t width, void *stream_) {
@@ -1214,8 +1391,25 @@ extern "C" int neptune_rt_run_steps(neptune_rt_stencil *s, neptune_rt_field *fa,
       local[0] = (s->tblock != 1 && ghost >= 2 * radius && own_e - own_b >= 4 * radius && tb2_eligible(s, cur, nxt, true, n_extra, extra)) ? 1 : 0;
       local[1] = own_e - own_b >= 2 * ghost ? 1 : 0;    // boundary planes and interior can be split
       local[2] = own_e - own_b >= ghost ? 1 : 0;        // the owned planes cover a whole halo
-      local[3] = 1;
+      // peer-to-peer exchange: every field that has ghost planes to refresh must be mappable on every rank (the swaps
+      // inside p2p_map_field are collective with the neighbours, so every rank makes them, able or not)
       cudaSetDevice(c->device);
+      bool p2p_ok = c->p2p;
+      {
+        const char *mode = std::getenv("NEPTUNE_RT_HALO");
+        if (!(mode && std::strcmp(mode, "nccl") == 0)) {
+          std::vector<neptune_rt_field *> fs = {fa, fb};
+          for (int k = 0; k < n_extra; ++k) fs.push_back(extra[k]);
+          for (neptune_rt_field *f : fs) {
+            bool ok = false;
+            if (int rc = p2p_map_field(c, f, own_b, own_e, ghost, &ok)) return rc;
+            p2p_ok = p2p_ok && ok;
+          }
+        } else {
+          p2p_ok = false;
+        }
+      }
+      local[3] = p2p_ok ? 1 : 0;
       if (!c->agree_dev) {
         RT_CUDA(c, cudaMalloc(&c->agree_dev, 4 * sizeof(int)));
         RT_CUDA(c, cudaMallocHost(&c->agree_host, 4 * sizeof(int)));
@@ -1231,13 +1425,14 @@ extern "C" int neptune_rt_run_steps(neptune_rt_stencil *s, neptune_rt_field *fa,
       ag.valid = true;
       ag.fuse2 = c->agree_host[0] != 0;
       ag.split = c->agree_host[1] != 0;
+      ag.p2p = c->agree_host[3] != 0;
       ag.a = fa; ag.b = fb;
       ag.extra.assign(extra, extra + n_extra);
       ag.tblock = s->tblock;
       ag.want_tb = s->want_tb;
     }
   }
-  const bool fuse2 = s->agreed.fuse2, split = s->agreed.split;
+  const bool fuse2 = s->agreed.fuse2, split = s->agreed.split, p2p = s->agreed.p2p;
 
   struct LoopGuard {   // dim-0 bounds of every launch below are the global apply bounds (ghost planes are computed too)
     neptune_rt_stencil *s;
@@ -1267,17 +1462,44 @@ extern "C" int neptune_rt_run_steps(neptune_rt_stencil *s, neptune_rt_field *fa,
     return NEPTUNE_RT_OK;
   };
 
+  // One exchange of the `ghost` boundary planes of f, started after the launch that produced them (sweep stream) and
+  // joined before the next launch that reads ghost planes.  p2p: copy engines + flags (no SM takes part: an NCCL
+  // send/recv kernel cannot become resident beside the persistent interior launch, which holds every SM's shared memory
+  // and registers — r02 trace: the NCCL exchange of a step pair completed only as the interior launch drained);
+  // otherwise ncclSend/ncclRecv.
+  uint32_t ex_epoch = 0;
+  auto exchange_start = [&](neptune_rt_field *f) -> int {
+    if (p2p) {
+      ex_epoch = ++c->epoch;
+      if (int rc = p2p_announce(c, ex_epoch)) return rc;
+    }
+    RT_CUDA(c, cudaEventRecord(c->ev_boundary, c->stream));
+    RT_CUDA(c, cudaStreamWaitEvent(c->halo_stream, c->ev_boundary, 0));
+    if (p2p) {
+      if (int rc = p2p_push(c, f, own_b, own_e, ghost, ex_epoch)) return rc;
+    } else {
+      if (int rc = neptune_rt_halo_exchange(c, f, own_b, own_e, ghost, c->halo_stream)) return rc;
+    }
+    if (int rc = trace_mark(2, c->halo_stream)) return rc;
+    RT_CUDA(c, cudaEventRecord(c->ev_halo, c->halo_stream));
+    return NEPTUNE_RT_OK;
+  };
+  auto exchange_join = [&]() -> int {
+    RT_CUDA(c, cudaStreamWaitEvent(c->stream, c->ev_halo, 0));   // my own copies / sends are done: the planes may be rewritten
+    if (p2p) return p2p_join(c, ex_epoch);                       // the neighbours' planes have arrived
+    return NEPTUNE_RT_OK;
+  };
+
   // every ghost plane of the first input state
-  RT_CUDA(c, cudaEventRecord(c->ev_boundary, c->stream));
-  RT_CUDA(c, cudaStreamWaitEvent(c->halo_stream, c->ev_boundary, 0));
-  if (int rc = neptune_rt_halo_exchange(c, cur, own_b, own_e, ghost, c->halo_stream)) return rc;
+  if (int rc = exchange_start(cur)) return rc;
+  if (int rc = exchange_join()) return rc;
   // launches that compute ghost planes read the other inputs (coefficients, right-hand side) there:
   // bring their ghost planes up to date once (they do not change over the time loop)
   if (ghost > radius || fuse2)
-    for (int k = 0; k < n_extra; ++k)
-      if (int rc = neptune_rt_halo_exchange(c, extra[k], own_b, own_e, ghost, c->halo_stream)) return rc;
-  RT_CUDA(c, cudaEventRecord(c->ev_halo, c->halo_stream));
-  RT_CUDA(c, cudaStreamWaitEvent(c->stream, c->ev_halo, 0));
+    for (int k = 0; k < n_extra; ++k) {
+      if (int rc = exchange_start(extra[k])) return rc;
+      if (int rc = exchange_join()) return rc;
+    }
   int64_t valid = ghost;   // ghost planes of `cur` that hold the neighbour's current state
   for (int64_t t = 0; t < nsteps;) {
     const bool two = fuse2 && t + 2 <= nsteps;
@@ -1297,12 +1519,8 @@ extern "C" int neptune_rt_run_steps(neptune_rt_stencil *s, neptune_rt_field *fa,
       // thin slab (agreed by all ranks): sweep, then exchange, not overlapped
       if (int rc = do_apply(s, d.n_inputs, ins, nxt, own_b, own_e, c->stream, two)) return rc;
       if (int rc = trace_mark(1, c->stream)) return rc;
-      RT_CUDA(c, cudaEventRecord(c->ev_boundary, c->stream));
-      RT_CUDA(c, cudaStreamWaitEvent(c->halo_stream, c->ev_boundary, 0));
-      if (int rc = neptune_rt_halo_exchange(c, nxt, own_b, own_e, ghost, c->halo_stream)) return rc;
-      if (int rc = trace_mark(2, c->halo_stream)) return rc;
-      RT_CUDA(c, cudaEventRecord(c->ev_halo, c->halo_stream));
-      RT_CUDA(c, cudaStreamWaitEvent(c->stream, c->ev_halo, 0));
+      if (int rc = exchange_start(nxt)) return rc;
+      if (int rc = exchange_join()) return rc;
       if (int rc = trace_mark(3, c->stream)) return rc;
       valid = ghost;
     } else {
@@ -1315,21 +1533,17 @@ extern "C" int neptune_rt_run_steps(neptune_rt_stencil *s, neptune_rt_field *fa,
         if (down) if (int rc = do_apply(s, d.n_inputs, ins, nxt, own_e - w, own_e, c->stream, two)) return rc;
       }
       if (int rc = trace_mark(1, c->stream)) return rc;
-      RT_CUDA(c, cudaEventRecord(c->ev_boundary, c->stream));
-      RT_CUDA(c, cudaStreamWaitEvent(c->halo_stream, c->ev_boundary, 0));
       // 2. halo exchange of the new state on the high-priority stream, concurrent with 3.
-      if (int rc = neptune_rt_halo_exchange(c, nxt, own_b, own_e, w, c->halo_stream)) return rc;
-      if (int rc = trace_mark(2, c->halo_stream)) return rc;
-      RT_CUDA(c, cudaEventRecord(c->ev_halo, c->halo_stream));
+      if (int rc = exchange_start(nxt)) return rc;
       // 3. interior
       if (int rc = do_apply(s, d.n_inputs, ins, nxt, own_b + (up ? w : 0), own_e - (down ? w : 0), c->stream, two)) return rc;
       if (int rc = trace_mark(3, c->stream)) return rc;
       // 4. join
-      RT_CUDA(c, cudaStreamWaitEvent(c->stream, c->ev_halo, 0));
+      if (int rc = exchange_join()) return rc;
       valid = ghost;
     }
     if (trace) { c->trace_kind.push_back((two ? 20 : 10) + (exchange ? 1 : 0)); c->trace_groups++; }
-    if (exchange) if (int rc = nccl_health()) return rc;
+    if (exchange && !p2p) if (int rc = nccl_health()) return rc;
     std::swap(cur, nxt);
     t += two ? 2 : 1;
   }
@@ -1360,6 +1574,11 @@ extern "C" int neptune_rt_slab_trace_read(neptune_rt_ctx *c, double *out, int ca
     if (kinds) kinds[g] = c->trace_kind[(size_t)g];
   }
   return c->trace_groups;
+}
+
+extern "C" const char *neptune_rt_stencil_halo_mode(neptune_rt_stencil *s) {
+  if (!s || !s->agreed.valid) return "";
+  return s->agreed.p2p ? "p2p" : "nccl";
 }
 
 extern "C" int neptune_rt_stencil_set_slab(neptune_rt_stencil *s, int64_t ghost, int64_t global_lb0, int64_t global_ub0) {

@@ -105,6 +105,7 @@ def lib() -> C.CDLL:
         "neptune_rt_slab_partition": (i32, [i64, i32, i32, i64p, i64p]),
         "neptune_rt_slab_localize": (i32, [C.POINTER(StencilDescC), i32, i32, i64, C.POINTER(StencilDescC), i64p, i64p]),
         "neptune_rt_stencil_set_slab": (i32, [vp, i64, i64, i64]),
+        "neptune_rt_stencil_halo_mode": (C.c_char_p, [vp]),
         "neptune_rt_comm_unique_id": (i32, [vp]),
         "neptune_rt_comm_init": (i32, [vp, vp, i32, i32]),
         "neptune_rt_halo_exchange": (i32, [vp, vp, i64, i64, i64, vp]),
@@ -430,6 +431,10 @@ class Stencil:
 
     def variant(self) -> str:
         return self.ctx._L.neptune_rt_stencil_variant(self.h).decode()
+
+    def halo_mode(self) -> str:
+        """'p2p' (copy engines + flags over NVLink), 'nccl', or '' before the first slab-mode run_steps."""
+        return self.ctx._L.neptune_rt_stencil_halo_mode(self.h).decode()
 
     def variants(self) -> List[str]:
         n = self.ctx._L.neptune_rt_stencil_variant_count(self.h)

@@ -34,7 +34,27 @@ def test_headers_are_plain_c(tmp_path):
 
 
 def test_library_holds_sm100a_tma_kernels(nb):
-    """The shipped .so must contain sm_100a SASS with TMA loads (UTMALDG), not a generic fallback."""
+    """The shipped .so holds sm_100a SASS whose staged kernels load through the Tensor Memory Accelerator (UTMALDG) and
+    synchronise on mbarriers (SYNCS); the bit-exact tier contains NO fused multiply-add (DFMA == 0) while its FMA twin
+    does; the default kernels read their windows with LDS, not generic loads (scripts/sass_census.py)."""
+    import sys
     out = subprocess.run(["cuobjdump", "-lelf", nb.runtime.LIB_PATH], stdout=subprocess.PIPE, text=True).stdout
     assert "sm_100a" in out
     assert ctypes.sizeof(nb.runtime.BodyOp) == 48
+    sys.path.insert(0, os.path.join(ROOT, "scripts"))
+    import sass_census as sc
+    key = "16c0ec9675fa5599"          # 3-D 7-point fp64 heat step (BASELINE configs[2])
+    syms = [s for s in sc.kernels_of() if key in s]
+    by = {}
+    for s in syms:
+        name = sc.demangle(s)
+        fam = name.split("neptune::")[1].split("<")[0]
+        fma = name.split("(")[0].rstrip(">").endswith("true")
+        by[(fam, fma)] = sc.census(s)
+    for fam in ("sweep_tma", "sweep_tb2", "sweep_tb2m", "sweep_tb2q"):
+        plain, fused = by[(fam, False)], by[(fam, True)]
+        assert plain["UTMALDG"] >= 1 and plain["SYNCS"] >= 10, (fam, plain)
+        assert plain["DFMA"] == 0 and plain["DADD"] > 0 and plain["DMUL"] > 0, (fam, plain)     # never contracted
+        assert fused["DFMA"] > 0, (fam, fused)
+        assert plain["LDS"] > 0, (fam, plain)
+    assert by[("sweep_direct", False)]["DFMA"] == 0 and by[("sweep_direct", True)]["DFMA"] > 0
