@@ -96,7 +96,10 @@ typedef struct neptune_rt_stencil neptune_rt_stencil;
 /* Replaces the lazy `neptune_rt_init_noargs` (NeptunePETScRuntime.h:47). device < 0 picks
  * LOCAL_RANK (or 0). */
 int neptune_rt_init(int device, neptune_rt_ctx **ctx);
+/* Releases the ctx AND every field / stencil created on it that the caller has not freed (their handles become
+ * invalid). neptune_rt_ctx_alive tells a handle owner that may outlive the ctx whether it still exists. */
 int neptune_rt_finalize(neptune_rt_ctx *ctx);
+int neptune_rt_ctx_alive(neptune_rt_ctx *ctx);
 int neptune_rt_sync(neptune_rt_ctx *ctx);
 /* Message of the last failure on this thread (ctx may be NULL for init failures). */
 const char *neptune_rt_last_error(neptune_rt_ctx *ctx);

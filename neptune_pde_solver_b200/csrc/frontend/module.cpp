@@ -523,6 +523,8 @@ extern "C" int neptune_b200_compile(const char *text, const char *pipeline, nept
 extern "C" int neptune_b200_module_destroy(neptune_b200_module *m) {
   if (!m) return NEPTUNE_RT_OK;
   for (auto &pc : m->per_ctx) {
+    // a ctx finalized before the module took its fields and stencils with it (neptune_rt_finalize): nothing left to free
+    if (!neptune_rt_ctx_alive(pc.first)) continue;
     for (auto *s : pc.second.stencils) neptune_rt_stencil_destroy(s);
     for (auto &kv : pc.second.arg_fields)
       for (auto *f : kv.second) neptune_rt_field_free(f);

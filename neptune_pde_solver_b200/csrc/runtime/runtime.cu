@@ -21,6 +21,7 @@
 #include <functional>
 #include <initializer_list>
 #include <memory>
+#include <set>
 #include <string>
 #include <vector>
 
@@ -92,6 +93,10 @@ NcclApi &nccl() {
 }
 
 thread_local std::string g_last_error;
+std::set<neptune_rt_ctx *> &live_ctxs() {
+  static std::set<neptune_rt_ctx *> s;
+  return s;
+}
 
 struct NvtxRange {   // ranges around the time loop and the host-memref sweep
   explicit NvtxRange(const char *name) { nvtxRangePushA(name); }
@@ -117,6 +122,10 @@ struct neptune_rt_ctx {
   std::string err;
   ncclComm_t comm = nullptr;
   int nranks = 1, rank = 0;
+  // every field and stencil created on this ctx and not yet freed: neptune_rt_finalize releases what is left, so a
+  // handle owner that outlives the ctx (a neptune_b200_module) must ask neptune_rt_ctx_alive before touching them
+  std::set<neptune_rt_field *> live_fields;
+  std::set<neptune_rt_stencil *> live_stencils;
   // slab mode: rank-local facts are agreed once per (stencil, fields) with a 4-int ncclAllReduce(min)
   int *agree_dev = nullptr, *agree_host = nullptr;
   // slab trace (neptune_rt_slab_trace): timing events of the last traced neptune_rt_run_steps
@@ -351,6 +360,7 @@ extern "C" int neptune_rt_init(int device, neptune_rt_ctx **out) {
   INIT_CUDA(cudaStreamCreateWithFlags(&c->h2d_stream, cudaStreamNonBlocking));
   INIT_CUDA(cudaStreamCreateWithFlags(&c->d2h_stream, cudaStreamNonBlocking));
 #undef INIT_CUDA
+  live_ctxs().insert(c);
   *out = c;
   return NEPTUNE_RT_OK;
 }
@@ -376,6 +386,10 @@ extern "C" int neptune_rt_finalize(neptune_rt_ctx *c) {
   cudaSetDevice(c->device);
   for (cudaStream_t st : {c->stream, c->halo_stream, c->h2d_stream, c->d2h_stream})
     if (st) cudaStreamSynchronize(st);
+  // what the caller did not free goes with the ctx (handles become invalid: neptune_rt_ctx_alive)
+  while (!c->live_stencils.empty()) neptune_rt_stencil_destroy(*c->live_stencils.begin());
+  while (!c->live_fields.empty()) neptune_rt_field_free(*c->live_fields.begin());
+  live_ctxs().erase(c);
   if (c->comm && nccl().ok) nccl().CommDestroy(c->comm);
   for (cudaEvent_t e : {c->ev_boundary, c->ev_halo, c->ev_t0, c->ev_t1})
     if (e) cudaEventDestroy(e);
@@ -394,6 +408,8 @@ extern "C" int neptune_rt_finalize(neptune_rt_ctx *c) {
   delete c;
   return NEPTUNE_RT_OK;
 }
+
+extern "C" int neptune_rt_ctx_alive(neptune_rt_ctx *c) { return c && live_ctxs().count(c) ? 1 : 0; }
 
 extern "C" int neptune_rt_sync(neptune_rt_ctx *c) {
   if (!c) return set_error(nullptr, NEPTUNE_RT_EINVAL, "neptune_rt_sync: NULL ctx");
@@ -434,12 +450,14 @@ extern "C" int neptune_rt_field_alloc(neptune_rt_ctx *c, int dtype, int rank, co
     return set_error(c, e == cudaErrorMemoryAllocation ? NEPTUNE_RT_ENOMEM : NEPTUNE_RT_ECUDA,
                      "cudaMalloc of a %zu-byte field failed: %s", (size_t)0 + f->bytes, cudaGetErrorString(e));
   }
+  c->live_fields.insert(f);
   *out = f;
   return NEPTUNE_RT_OK;
 }
 
 extern "C" int neptune_rt_field_free(neptune_rt_field *f) {
   if (!f) return NEPTUNE_RT_OK;
+  f->ctx->live_fields.erase(f);
   cudaSetDevice(f->ctx->device);
   // the halo, upload and download streams may still be reading or writing this field
   for (cudaStream_t st : {f->ctx->halo_stream, f->ctx->h2d_stream, f->ctx->stream, f->ctx->d2h_stream})
@@ -477,6 +495,7 @@ extern "C" int neptune_rt_field_wrap_device(neptune_rt_ctx *c, int dtype, int ra
   canon_box(rank, lb, ub, clb, f->ext);
   f->bytes = (size_t)f->numel() * f->elsize();
   f->dptr = device_ptr;
+  c->live_fields.insert(f);
   *out = f;
   return NEPTUNE_RT_OK;
 }
@@ -661,11 +680,13 @@ extern "C" int neptune_rt_stencil_create(neptune_rt_ctx *c, const neptune_rt_ste
   s->info = neptune::analyze_body(s->desc.c);
   s->body = be;
   s->fma = (d->flags & NEPTUNE_RT_FLAG_FMA) != 0;
+  c->live_stencils.insert(s);
   *out = s;
   return NEPTUNE_RT_OK;
 }
 
 extern "C" int neptune_rt_stencil_destroy(neptune_rt_stencil *s) {
+  if (s && s->ctx) s->ctx->live_stencils.erase(s);
   delete s;
   return NEPTUNE_RT_OK;
 }

@@ -70,6 +70,7 @@ def lib() -> C.CDLL:
     sig = {
         "neptune_rt_init": (i32, [i32, C.POINTER(vp)]),
         "neptune_rt_finalize": (i32, [vp]),
+        "neptune_rt_ctx_alive": (i32, [vp]),
         "neptune_rt_sync": (i32, [vp]),
         "neptune_rt_last_error": (C.c_char_p, [vp]),
         "neptune_rt_launch_count": (i64, [vp]),
@@ -401,7 +402,8 @@ class Field:
 
     def free(self):
         if self.h:
-            self.ctx._L.neptune_rt_field_free(self.h)
+            if self.ctx.h:            # a closed ctx released its fields itself (neptune_rt_finalize)
+                self.ctx._L.neptune_rt_field_free(self.h)
             self.h = None
 
 
@@ -467,7 +469,7 @@ class Stencil:
         return a if res.value == a.h.value else b
 
     def destroy(self):
-        if self.h and self._owned:
+        if self.h and self._owned and self.ctx.h:
             self.ctx._L.neptune_rt_stencil_destroy(self.h)
         self.h = None
 
