@@ -78,6 +78,28 @@ def program_for(kind, shape, ty, alpha, h2, lb=None):
 PARITY_STEPS = 4
 
 
+class BandRows:
+    """The few dim-0 rows of a big host array that the band parity check reads (so that 27 coefficient fields of 1 GB
+    each need not stay in host memory): rows [r0, r1) are kept for every range asked for at construction."""
+
+    def __init__(self, a, ranges):
+        self.shape, self.ndim, self.dtype = a.shape, a.ndim, a.dtype
+        self.parts = {(r0, r1): np.array(a[r0:r1], copy=True) for (r0, r1) in ranges}
+
+    def __getitem__(self, key):
+        rows, rest = key[0], key[1:]
+        return self.parts[(rows.start, rows.stop)][(slice(None),) + tuple(rest)]
+
+
+def band_row_ranges(world, own_rows):
+    ob, oe = own_rows
+    S = PARITY_STEPS
+    if world == 1:
+        mid = (ob + oe) // 2
+        return [(mid - 2 * S, mid + 2 * S)]
+    return [(ob, ob + 2 * S), (oe - 2 * S, oe)]
+
+
 def band_parity_check(kind, ty, alpha, h2, world, rank, own_rows, u_local, extra_local, run_fn, gather_fn):
     """Bitwise parity inside the benchmark run, on the ACTUAL configuration (kernel variant, slab decomposition,
     ghost depth, NCCL exchange): 4 steps from the benchmark's initial state, then an 8-plane band that straddles
@@ -374,7 +396,8 @@ def run_b200(args):
         ctx.sync()
         extra.append(f)
         if not args.no_parity:
-            extra_host.append(c)
+            extra_host.append(BandRows(c, band_row_ranges(world, slab.own_rows if world > 1 else (0, lshape[0]))))
+        del c
 
     def barrier():
         ctx.sync()
