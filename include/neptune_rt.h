@@ -227,6 +227,16 @@ int neptune_rt_slab_localize(const neptune_rt_stencil_desc *global_desc, int nra
  * alignment) are agreed by all ranks with one small ncclAllReduce per (fields, settings). */
 int neptune_rt_stencil_set_slab(neptune_rt_stencil *stencil, int64_t ghost, int64_t global_lb0,
                                 int64_t global_ub0);
+/* The launch plan neptune_rt_run_steps follows in slab mode, as data (pure host code; the time loop itself calls the same
+ * function): launch i advances plan[i].steps time steps (2 where two steps fuse) over the owned planes extended by
+ * plan[i].ext ghost planes on every side that has a neighbour — computed redundantly with the neighbour, bit for bit
+ * the same arithmetic — and when plan[i].exchange is set its `ghost` owned boundary planes are exchanged after it
+ * (computed first, the exchange overlapping the interior). With G ghost planes that is one exchange per
+ * G / (radius * steps per launch) launches. Returns the number of launches, or -1 for impossible arguments; writes at
+ * most `capacity` entries. */
+typedef struct neptune_rt_slab_launch { int32_t steps; int32_t exchange; int64_t ext; } neptune_rt_slab_launch;
+int64_t neptune_rt_slab_schedule(int64_t nsteps, int64_t radius, int64_t ghost, int fuse2,
+                                 neptune_rt_slab_launch *plan, int64_t capacity);
 /* How the last slab-mode neptune_rt_run_steps of this stencil exchanged ghost planes ("" before the first):
  *   "p2p"  — the default between GPUs of one node: every rank PUSHES its boundary planes into the neighbour's field
  *            memory (CUDA IPC mapping) with a copy engine over NVLink, ordered by stream memory operations

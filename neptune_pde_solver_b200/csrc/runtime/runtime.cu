@@ -1352,6 +1352,36 @@ extern "C" int neptune_rt_halo_exchange(neptune_rt_ctx *c, neptune_rt_field *f, 
 // ---------------------------------------------------------------------------------------------
 // time loop
 // ---------------------------------------------------------------------------------------------
+namespace {
+// One launch of the slab time loop: `valid` ghost planes hold the neighbours' current state going in.  A launch that
+// advances T steps consumes T * radius of them; it also computes the ghost planes that stay valid afterwards (ext),
+// unless the next launch would run short — then it computes the owned planes only and its result is exchanged.
+neptune_rt_slab_launch slab_next(int64_t t, int64_t nsteps, int64_t radius, bool fuse2, int64_t valid) {
+  neptune_rt_slab_launch L;
+  const bool two = fuse2 && t + 2 <= nsteps;
+  const int64_t adv = two ? 2 * radius : radius;          // ghost planes this launch consumes
+  const int64_t left = nsteps - t - (two ? 2 : 1);        // steps after this launch
+  const int64_t adv_next = (fuse2 && left >= 2) ? 2 * radius : radius;
+  L.steps = two ? 2 : 1;
+  L.exchange = (left > 0 && valid - adv < adv_next) ? 1 : 0;
+  L.ext = (!L.exchange && left > 0) ? valid - adv : 0;
+  return L;
+}
+}  // namespace
+
+extern "C" int64_t neptune_rt_slab_schedule(int64_t nsteps, int64_t radius, int64_t ghost, int fuse2, neptune_rt_slab_launch *plan,
+                                            int64_t capacity) {
+  if (nsteps < 0 || radius < 0 || ghost < radius || (fuse2 && ghost < 2 * radius)) return -1;
+  int64_t n = 0, valid = ghost;
+  for (int64_t t = 0; t < nsteps; ++n) {
+    const neptune_rt_slab_launch L = slab_next(t, nsteps, radius, fuse2 != 0, valid);
+    if (plan && n < capacity) plan[n] = L;
+    valid = L.exchange ? ghost : valid - L.steps * radius;
+    t += L.steps;
+  }
+  return n;
+}
+
 extern "C" int neptune_rt_run_steps(neptune_rt_stencil *s, neptune_rt_field *fa, neptune_rt_field *fb, int n_extra,
                                     neptune_rt_field *const *extra, int64_t nsteps, neptune_rt_field **result) {
   if (!s || !fa || !fb) return set_error(s ? s->ctx : nullptr, NEPTUNE_RT_EINVAL, "run_steps: NULL argument");
@@ -1523,16 +1553,14 @@ extern "C" int neptune_rt_run_steps(neptune_rt_stencil *s, neptune_rt_field *fa,
     }
   int64_t valid = ghost;   // ghost planes of `cur` that hold the neighbour's current state
   for (int64_t t = 0; t < nsteps;) {
-    const bool two = fuse2 && t + 2 <= nsteps;
-    const int64_t adv = two ? 2 * radius : radius;          // ghost planes this launch consumes
-    const int64_t left = nsteps - t - (two ? 2 : 1);        // steps after this launch
-    const int64_t adv_next = (fuse2 && left >= 2) ? 2 * radius : radius;
-    const bool exchange = left > 0 && valid - adv < adv_next;
+    const neptune_rt_slab_launch L = slab_next(t, nsteps, radius, fuse2, valid);   // the plan neptune_rt_slab_schedule prints
+    const bool two = L.steps == 2, exchange = L.exchange != 0;
+    const int64_t adv = L.steps * radius;
     ins[0] = cur;
     if (int rc = trace_mark(0, c->stream)) return rc;
     if (!exchange) {
       // one launch over the owned planes plus the ghost planes that stay valid
-      const int64_t ext = left > 0 ? valid - adv : 0;
+      const int64_t ext = L.ext;
       if (int rc = do_apply(s, d.n_inputs, ins, nxt, own_b - (up ? ext : 0), own_e + (down ? ext : 0), c->stream, two)) return rc;
       valid -= adv;
       if (trace) { for (int w = 1; w < 4; ++w) if (int rc = trace_mark(w, c->stream)) return rc; }

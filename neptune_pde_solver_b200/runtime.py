@@ -107,6 +107,7 @@ def lib() -> C.CDLL:
         "neptune_rt_slab_localize": (i32, [C.POINTER(StencilDescC), i32, i32, i64, C.POINTER(StencilDescC), i64p, i64p]),
         "neptune_rt_stencil_set_slab": (i32, [vp, i64, i64, i64]),
         "neptune_rt_stencil_halo_mode": (C.c_char_p, [vp]),
+        "neptune_rt_slab_schedule": (i64, [i64, i64, i64, i32, vp, i64]),
         "neptune_rt_comm_unique_id": (i32, [vp]),
         "neptune_rt_comm_init": (i32, [vp, vp, i32, i32]),
         "neptune_rt_halo_exchange": (i32, [vp, vp, i64, i64, i64, vp]),
@@ -248,6 +249,20 @@ def slab_localize(desc: StencilDesc, nranks: int, rank: int, halo: int) -> Stenc
     if rc:
         raise NeptuneError(rc, lib().neptune_rt_last_error(None).decode())
     return StencilDesc.from_c(l)
+
+
+class SlabLaunch(C.Structure):
+    _fields_ = [("steps", C.c_int32), ("exchange", C.c_int32), ("ext", C.c_int64)]
+
+
+def slab_schedule(nsteps: int, radius: int, ghost: int, fuse2: bool):
+    """The launch plan of neptune_rt_run_steps in slab mode: [(steps, ext, exchange)] per launch."""
+    n = lib().neptune_rt_slab_schedule(nsteps, radius, ghost, int(fuse2), None, 0)
+    if n < 0:
+        raise NeptuneError(EINVAL, "slab_schedule: impossible arguments")
+    plan = (SlabLaunch * max(1, n))()
+    lib().neptune_rt_slab_schedule(nsteps, radius, ghost, int(fuse2), plan, n)
+    return [(plan[i].steps, plan[i].ext, bool(plan[i].exchange)) for i in range(n)]
 
 
 def comm_unique_id() -> bytes:
