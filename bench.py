@@ -592,8 +592,8 @@ def run_b200(args):
                 r.download_planes(hargs[0], 0, lshape[0])
                 ctx.sync()
                 hargs[0], hargs[1] = hargs[1], hargs[0]
-            api = ("per rank: neptune_rt_field_upload(local box, pinned) + neptune_rt_run_steps(1 step, slab mode, NCCL halo exchange) + "
-                   "neptune_rt_field_download; not pipelined")
+            api = ("per rank: neptune_rt_field_upload(local box, pinned) + neptune_rt_run_steps(1 step, slab mode, halo exchange included) + "
+                   "neptune_rt_field_download; not pipelined; halo mode " + stencil.halo_mode())
         for _ in range(2):
             e2e_step()
         barrier()
