@@ -181,8 +181,13 @@ template <class F> struct BodyRegistrar {
         e.variants.push_back(item_variant<F, TmaK<F, Tile3W, false>, false>("tma:64x8"));
         e.variants.push_back(item_variant<F, TmaK<F, Tile3W, true>, true>("tma:64x8"));
       } else if constexpr (F::RZ > 0) {
-        e.variants.push_back(item_variant<F, TmaK<F, Tile3A, false>, false>("tma:64x16"));
-        e.variants.push_back(item_variant<F, TmaK<F, Tile3A, true>, true>("tma:64x16"));
+        if constexpr (F::NIN == 1) {   // ring read through generic pointers: measured faster for single-input bodies (tiles.cuh)
+          e.variants.push_back(item_variant<F, TmaK<F, Tile3Ag, false>, false>("tma:64x16"));
+          e.variants.push_back(item_variant<F, TmaK<F, Tile3Ag, true>, true>("tma:64x16"));
+        } else {
+          e.variants.push_back(item_variant<F, TmaK<F, Tile3A, false>, false>("tma:64x16"));
+          e.variants.push_back(item_variant<F, TmaK<F, Tile3A, true>, true>("tma:64x16"));
+        }
         if constexpr (F::NIN == 1 && F::RZ == 1) {
           e.variants.push_back(item_variant<F, Tb2K<F, Tb2A, false>, false>("tb2:64x16"));      // boxes narrower than 256
           e.variants.push_back(item_variant<F, Tb2K<F, Tb2A, true>, true>("tb2:64x16"));

@@ -35,9 +35,10 @@ typedef CUtensorMap_st CUtensorMap;
 
 namespace neptune {
 
-template <int TX_, int TY_, int VY_, int NS_, int MINB_, bool STREAM_ = false> struct TileCfg {
+template <int TX_, int TY_, int VY_, int NS_, int MINB_, bool STREAM_ = false, bool GENERIC_ = false> struct TileCfg {
   static constexpr int TX = TX_, TY = TY_, VY = VY_, NS = NS_, MINB = MINB_;
-  static constexpr bool STREAM = STREAM_;  // results leave with st.global.cs (evict-first in L2)
+  static constexpr bool STREAM = STREAM_;    // results leave with st.global.cs (evict-first in L2)
+  static constexpr bool GENERIC = GENERIC_;  // ring read through generic pointers (LD.E) instead of LDS: see the kernel
 };
 
 template <class F, class C> struct TmaGeom {
@@ -184,7 +185,8 @@ sweep_tma(const __grid_constant__ KParams<F> p, const __grid_constant__ CUtensor
   extern __shared__ __align__(128) unsigned char smem_raw[];
   // (pointer arithmetic, not a round trip through an integer: the latter loses the shared address space and every
   // window read became a generic LD.E instead of LDS — r02 SASS census)
-  unsigned char *smem = smem_raw + ((128u - (smem_u32(smem_raw) & 127u)) & 127u);
+  unsigned char *smem = C::GENERIC ? reinterpret_cast<unsigned char *>((reinterpret_cast<uintptr_t>(smem_raw) + 127) & ~uintptr_t(127))
+                                   : smem_raw + ((128u - (smem_u32(smem_raw) & 127u)) & 127u);
   const uint32_t full0 = smem_u32(smem + NS * G::STAGE_BYTES);  // full[s]: TMA bytes of stage s have landed
   const uint32_t empty0 = full0 + 8 * NS;                       // empty[s]: every consumer warp is done with stage s
   const uint32_t stage0 = smem_u32(smem);

@@ -13,6 +13,10 @@ namespace neptune {
 
 // 3-D bodies march in z; bodies without z taps (2-D) take bigger tiles.  (TX, TY, VY, ring stages, min CTAs per SM)
 typedef TileCfg<64, 16, 2, 8, 2> Tile3A;      // r01 sweep on C3: 0.87 of the measured copy peak
+// The same tile with the ring read through generic pointers (LD.E) instead of LDS.  Measured A/B in one session (r02,
+// profiles/r02_tma_lds_vs_generic.txt): single-input 7-point body on C3 344.5 (generic) vs 326.0 (LDS) Gupd/s; with a
+// pointwise input (C5) 205.4 vs 210.1; 27 coefficient fields (C4) 24.3 vs 24.6.  Single-input bodies take the generic form.
+typedef TileCfg<64, 16, 2, 8, 2, false, true> Tile3Ag;
 typedef TileCfg<64, 8, 1, 6, 1> Tile3W;       // many-input bodies (one coefficient field per tap)
 typedef TileCfg<128, 32, 8, 3, 2> Tile2A;
 typedef Tb2Cfg<64, 16, 2, 5, 2> Tb2A;         // two time steps per launch, both levels through shared memory (sweep_tb2.cuh)

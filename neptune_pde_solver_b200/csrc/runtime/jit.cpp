@@ -155,7 +155,8 @@ std::vector<KernelSpec> kernel_menu(const neptune_rt_stencil_desc &d, const Body
     if (d.n_inputs > 4) {
       for (bool fma : {false, true}) add("tma:64x8", VARIANT_TMA, fma, "sweep_tma", "TmaGeom", "Tile3W", G_TMA, JL_TILE, 1, 0, rz, true, false);
     } else if (rz > 0) {
-      for (bool fma : {false, true}) add("tma:64x16", VARIANT_TMA, fma, "sweep_tma", "TmaGeom", "Tile3A", G_TMA, JL_TILE, 1, 0, rz, true, false);
+      for (bool fma : {false, true})
+        add("tma:64x16", VARIANT_TMA, fma, "sweep_tma", "TmaGeom", d.n_inputs == 1 ? "Tile3Ag" : "Tile3A", G_TMA, JL_TILE, 1, 0, rz, true, false);
       if (d.n_inputs == 1 && rz == 1) {
         add("tb2:64x16", VARIANT_TB2, false, "sweep_tb2", "Tb2Geom", "Tb2A", G_TB2, JL_TILE, 2, 0, 2, true, false);
         if (zstar) {

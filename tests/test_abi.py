@@ -56,5 +56,6 @@ def test_library_holds_sm100a_tma_kernels(nb):
         assert plain["UTMALDG"] >= 1 and plain["SYNCS"] >= 10, (fam, plain)
         assert plain["DFMA"] == 0 and plain["DADD"] > 0 and plain["DMUL"] > 0, (fam, plain)     # never contracted
         assert fused["DFMA"] > 0, (fam, fused)
-        assert plain["LDS"] > 0, (fam, plain)
+        if fam != "sweep_tma":     # sweep_tma reads its ring through generic pointers for single-input bodies (measured faster, tiles.cuh)
+            assert plain["LDS"] > 0, (fam, plain)
     assert by[("sweep_direct", False)]["DFMA"] == 0 and by[("sweep_direct", True)]["DFMA"] > 0
