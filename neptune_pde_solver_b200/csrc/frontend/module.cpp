@@ -462,6 +462,20 @@ extern "C" int neptune_b200_compile(const char *text, const char *pipeline, nept
             r.function = fn.name;
             r.ap = op.apply.get();
             r.desc = recognize_apply(*op.apply, fma);
+            if (fn.kind == "linear_opdef") {
+              // the linear-region rule of the reference's verifier (VerifyAndAnnotate.cpp:183-204): a product needs a
+              // constant factor, a quotient a constant divisor
+              const neptune_rt_stencil_desc &d = r.desc.c;
+              for (int i = 0; i < d.n_ops; ++i) {
+                const neptune_rt_body_op &o = d.ops[i];
+                if (o.opcode == NEPTUNE_RT_OP_MUL && d.ops[o.a].opcode != NEPTUNE_RT_OP_CONST && d.ops[o.b].opcode != NEPTUNE_RT_OP_CONST)
+                  throw Diagnostic("line " + std::to_string(op.line) + ": MulFOp in linear region must multiply by a constant (apply inside " +
+                                   fn.name + ", a linear_opdef)");
+                if (o.opcode == NEPTUNE_RT_OP_DIV && d.ops[o.b].opcode != NEPTUNE_RT_OP_CONST)
+                  throw Diagnostic("line " + std::to_string(op.line) + ": DivFOp in linear region must divide by a constant (apply inside " +
+                                   fn.name + ", a linear_opdef)");
+              }
+            }
             r.cuda_source = generate_functor(r.desc.c);
             recs.push_back(std::move(r));
           }

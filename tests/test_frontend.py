@@ -205,3 +205,22 @@ def test_fusion_is_refused_when_it_would_change_the_result(nb):
             continue            # unfused AXPY-at-an-offset body is not in the catalogue: loud, not wrong
         assert "fused into one sweep" not in m.plan("@entry")
         m.destroy()
+
+
+def test_linear_opdef_rule_products_need_a_constant_factor(nb):
+    """checkApplyLike(requireLinearBody) of the reference (VerifyAndAnnotate.cpp:183-204): inside a linear_opdef a mulf
+    must have a constant operand and a divf a constant divisor.  The offending operator is rejected with the reference's
+    wording, the rest of the module still lowers; the same body in a func.func (variable coefficients) is legal."""
+    import json
+    import os
+    pack = json.load(open(os.path.join(os.path.dirname(__file__), "golden", "reference_inputs.json")))
+    text = pack["files"]["smoke_time_advance.mlir"]["text"]
+    assert "%t  = arith.mulf %alpha, %lap0 : f64" in text
+    bad = text.replace("%t  = arith.mulf %alpha, %lap0 : f64", "%t  = arith.mulf %x0, %lap0 : f64")
+    m = nb.Module(bad)
+    assert m.diagnostic("@ac_lap") is None
+    assert "MulFOp in linear region must multiply by a constant" in m.diagnostic("@ac_A")
+    m.destroy()
+    m = nb.Module(H.program("varcoef_3d7", [8, 8, 8])[0])       # mulf(access, access) in a func.func: fine
+    assert m.diagnostic("@entry") is None
+    m.destroy()
