@@ -12,7 +12,7 @@ import helpers as H  # noqa: E402
 import neptune_pde_solver_b200 as nb  # noqa: E402
 
 ctx = nb.Context(0)
-CASES = [("heat_star", (20, 30, 136), ["tma:64x16", "tb2:64x16", "tb2m:128x14", "tb2g:128x14"]),
+CASES = [("heat_star", (36, 30, 264), ["tma:64x16", "tb2:64x16", "tb2m:128x14", "tb2q:128x14"]),
          ("heat_box_2d9", (40, 1040), ["rows:512", "tb2r:256x3"]),
          ("jacobi_star", (20, 30, 72), ["tma:64x16", "tb2m:64x24"]),
          ("varcoef_3d27", (8, 12, 64), ["tma:64x8"])]
