@@ -133,3 +133,62 @@ def test_jacobi_1000_iterations_slabs_bit_exact(ty):
         assert p.exitcode == 0
     ok, used = q.get(timeout=5)
     assert ok is True and used.startswith("tb2"), used
+
+
+def _worker_mode(rank, world, port, q):
+    """Reports how the slab loop exchanged and its timeline (neptune_rt_stencil_halo_mode, neptune_rt_slab_trace)."""
+    import torch
+    import torch.distributed as dist
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    torch.cuda.set_device(rank)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        import neptune_pde_solver_b200 as nb
+        from neptune_pde_solver_b200.slab import Slab
+        shape = (64, 32, 256)
+        gtext, _ = H.program("heat_star", list(shape))
+        u, _ = H.inputs(shape, 0, "f64", seed=5)
+        s = Slab(nb.Module(gtext).apply_desc(0), world, rank, 4)
+        ctx = nb.Context(rank)
+        uid = [nb.comm_unique_id() if rank == 0 else None]
+        dist.broadcast_object_list(uid, src=0)
+        ctx.comm_init(uid[0], world, rank)
+        st = s.stencil(ctx)
+        lb, ub = s.local.out_lb, s.local.out_ub
+        fa, fb = nb.Field(ctx, np.float64, lb, ub), nb.Field(ctx, np.float64, lb, ub)
+        loc = s.scatter(u)
+        fa.upload(loc)
+        fb.upload(loc)
+        assert st.halo_mode() == ""
+        ctx.slab_trace(True)
+        st.run_steps(fa, fb, [], 8)
+        rows = ctx.slab_trace_read()
+        ctx.slab_trace(False)
+        plan = nb.runtime.slab_schedule(8, 1, 4, True)
+        if rank == 0:
+            q.put((st.halo_mode(), [r[0] for r in rows], [10 * p[0] + int(p[2]) for p in plan],
+                   all(r[1] <= r[2] <= r[4] + 1e-3 and r[1] <= r[3] for r in rows)))
+        fa.free(); fb.free()
+        ctx.close()
+    finally:
+        dist.destroy_process_group()
+
+
+def test_slab_loop_reports_its_exchange_mode_and_timeline():
+    import torch
+    import torch.multiprocessing as mp
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs >= 2 GPUs")
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_worker_mode, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    for p in procs:
+        p.join(300)
+        assert p.exitcode == 0
+    mode, kinds, planned, ordered = q.get(timeout=5)
+    assert mode == ("nccl" if os.environ.get("NEPTUNE_RT_HALO") == "nccl" else "p2p")   # GPUs of one node: copy engines + flags
+    assert kinds == planned          # the loop followed neptune_rt_slab_schedule: [20, 21, 20, 20] for 8 steps, 4 ghost planes
+    assert ordered
