@@ -150,6 +150,49 @@ int neptune_rt_field_store(neptune_rt_field *dst, neptune_rt_field *src, const i
 int neptune_rt_field_reduce_sum(neptune_rt_field *field, const int64_t *lb, const int64_t *ub,
                                 int allreduce, double *result);
 
+/* The same box sum for callers that must not allocate. It has no counterpart in the reference: the
+ * reference's reduce is a loop nest over a memref somebody else allocated, so the question never arises
+ * there; it arises here because neptune_rt_field_reduce_sum cudaMallocs its partial-sum scratch (and a
+ * pinned result word) on first use.
+ *
+ * Who needs this: a solver that owns the GPU's memory (PETSc-style pools sized at start-up, a framework's
+ * caching allocator that has already reserved all of HBM, so a cudaMalloc from a library fails), compiler-
+ * generated code whose buffers all come from its own bufferisation, and any inner loop that cannot afford
+ * the device-wide synchronisation cudaMalloc/cudaFree imply (one first-use allocation inside an iteration
+ * stalls the halo/interior overlap of the time step around it). This entry point takes no ctx and no field
+ * handle, calls no cudaMalloc / cudaFree / cudaMallocHost nor any routine that does, and keeps its partial
+ * sums in a static device array inside the library image: NEPTUNE_RT_REDUCE_STATIC_SCRATCH_BYTES bytes on
+ * every GPU that loads the library, held until the process exits.
+ *
+ *   src         device pointer to a dense row-major array of `shape` (rank 1..3), dtype NEPTUNE_RT_F32/F64
+ *   lb, ub      zero-based sub-box [lb, ub) of that array to sum; NULL = the whole array; an empty box sums to 0
+ *   result_dev  device pointer, 8-byte aligned, caller-owned: receives the sum as a double (an f32 array's
+ *               sum is rounded to f32 first, as neptune_rt_field_reduce_sum reports it)
+ *   stream      a cudaStream_t (NULL = the default stream). The call only enqueues two kernels; it does not
+ *               wait for them and copies nothing to the host.
+ *
+ * src and result_dev must belong to the CURRENT device (cudaSetDevice before the call); anything else is
+ * NEPTUNE_RT_EINVAL. Same partition and same fixed trees as neptune_rt_field_reduce_sum, hence the same value
+ * bit for bit, run to run.
+ *
+ * Limits: the scratch is one slot per CTA and does not grow with the box, so there is no element-count
+ * limit; what is limited is what the kernel indexes in 32 bits: every shape[d] must be
+ * <= NEPTUNE_RT_REDUCE_STATIC_MAX_EXTENT (2^30). A larger axis is refused with NEPTUNE_RT_EINVAL and a
+ * message (neptune_rt_last_error(NULL)) naming the axis and the limit; fold the axis into two, or use
+ * neptune_rt_field_reduce_sum. Device ordinals above 63 are NEPTUNE_RT_EUNSUPPORTED.
+ *
+ * Shared state: there is ONE scratch array per GPU for the whole process. Two calls that can run on the
+ * same GPU at the same time (different streams, different threads) race on it and may both return garbage:
+ * order them (same stream, or an event between them). The array keeps whatever the last call left in it;
+ * that is harmless, because each call overwrites every slot before reading any, and nothing needs clearing.
+ * The first call on each device looks the array's device address up (cudaGetSymbolAddress, which can make
+ * the CUDA runtime load the library's module on that device); make that first call during set-up, before
+ * any stream capture on that device. */
+#define NEPTUNE_RT_REDUCE_STATIC_SCRATCH_BYTES 4736 /* 592 partial sums (4 CTAs per SM x 148 SMs) x 8 bytes */
+#define NEPTUNE_RT_REDUCE_STATIC_MAX_EXTENT 1073741824LL
+int neptune_rt_reduce_sum_static(const void *src, int dtype, int rank, const int64_t *shape,
+                                 const int64_t *lb, const int64_t *ub, double *result_dev, void *stream);
+
 /* ---- stencils -------------------------------------------------------------------------- */
 /* 64-bit structure key of a body (constants' values, bounds and extents excluded): two applies
  * with the same key run the same compiled kernel. Pure host code. */

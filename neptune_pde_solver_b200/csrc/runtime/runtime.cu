@@ -21,6 +21,7 @@
 #include <functional>
 #include <initializer_list>
 #include <memory>
+#include <mutex>
 #include <set>
 #include <string>
 #include <vector>
@@ -1899,3 +1900,121 @@ extern "C" void _mlir_ciface_neptune_rt_call_input_3d(void *c, int32_t k, const 
 extern "C" void _mlir_ciface_neptune_rt_call_run_1d(void *c, const neptune_rt_memref_1d *o) { call_run<1>(c, o); }
 extern "C" void _mlir_ciface_neptune_rt_call_run_2d(void *c, const neptune_rt_memref_2d *o) { call_run<2>(c, o); }
 extern "C" void _mlir_ciface_neptune_rt_call_run_3d(void *c, const neptune_rt_memref_3d *o) { call_run<3>(c, o); }
+
+// ---------------------------------------------------------------------------------------------
+// neptune_rt_reduce_sum_static — the box sum for callers that may not allocate (include/neptune_rt.h).
+//
+// neptune_rt_field_reduce_sum keeps its per-CTA partial sums in ctx scratch that it cudaMallocs on
+// first use, and hands the result back through a cudaMallocHost'ed double. That is fine for a program
+// that lets this library own memory. It is not fine for the callers this path is bolted on to: a
+// Krylov solver (PETSc in the reference) that takes a norm or a dot product every iteration out of a
+// device pool it sized itself at start-up and filled to the last byte, code emitted by a compiler
+// pipeline whose every buffer comes from its own bufferisation, and a slab time loop that must not be
+// stalled half-way through (cudaMalloc and cudaFree synchronise the whole device, so a first-use
+// allocation inside a solver iteration also breaks the halo/interior overlap of the step around it).
+// For them the partial sums live in the array below: part of the library image, so it is in place as
+// soon as a GPU has loaded the module and stays until the process exits, and this entry point never
+// asks CUDA (or anyone else) for memory. No ctx, no field handle: plain pointers in, a device double out.
+//
+// Shared state, so the rules are: one array per GPU for the whole process; calls that can overlap on
+// one GPU (different streams, different host threads) race on it and must be ordered by the caller;
+// nothing in it has to be zero beforehand because every call's first kernel writes all
+// REDUCE_BLOCKS slots (a CTA without rows writes 0.0) before the second kernel reads them, so whatever
+// the previous call left behind is overwritten, never summed.
+// ---------------------------------------------------------------------------------------------
+namespace {
+static __device__ __align__(256) double g_reduce_static_scratch[REDUCE_BLOCKS];
+static_assert(sizeof(double) * REDUCE_BLOCKS == NEPTUNE_RT_REDUCE_STATIC_SCRATCH_BYTES,
+              "include/neptune_rt.h states the size of the static reduce scratch");
+
+constexpr int STATIC_SCRATCH_MAX_DEVICES = 64;
+// g_reduce_static_scratch in HOST code is only a handle for the runtime's symbol table, not an address a kernel can
+// use: the device address is looked up once per GPU, with that GPU current, and kept here.
+double *g_reduce_static_addr[STATIC_SCRATCH_MAX_DEVICES] = {};
+std::mutex g_reduce_static_mutex;
+
+// Same arithmetic as reduce_sum_final; the f32 rounding neptune_rt_field_reduce_sum does on the host after its
+// download happens here, because this variant leaves the result on the device.
+__global__ void __launch_bounds__(REDUCE_THREADS) reduce_sum_final_static(const double *__restrict__ partials, int n,
+                                                                          double *__restrict__ out, int round_to_f32) {
+  __shared__ double sh[REDUCE_THREADS / 32];
+  double acc = 0.0;
+  for (int i = threadIdx.x; i < n; i += REDUCE_THREADS) acc += partials[i];
+  const double t = block_sum_256(acc, sh);
+  if (threadIdx.x == 0) *out = round_to_f32 ? (double)(float)t : t;
+}
+
+// Device address of the scratch array on the CURRENT device (first use per device: symbol lookup, which also makes
+// the runtime load this module on that device if it has not yet).
+int reduce_static_scratch(int device, double **out) {
+  std::lock_guard<std::mutex> lock(g_reduce_static_mutex);
+  if (!g_reduce_static_addr[device]) {
+    void *p = nullptr;
+    cudaError_t e = cudaGetSymbolAddress(&p, g_reduce_static_scratch);
+    if (e != cudaSuccess || !p)
+      return set_error(nullptr, NEPTUNE_RT_ECUDA, "reduce_sum_static: cudaGetSymbolAddress of the scratch array failed on device %d: %s",
+                       device, cudaGetErrorString(e));
+    g_reduce_static_addr[device] = (double *)p;
+  }
+  *out = g_reduce_static_addr[device];
+  return NEPTUNE_RT_OK;
+}
+
+// A pointer the kernels may dereference on `device`: device or managed memory of that GPU.
+bool usable_on_device(const void *p, int device) {
+  cudaPointerAttributes a;
+  if (cudaPointerGetAttributes(&a, p) != cudaSuccess) { cudaGetLastError(); return false; }
+  if (a.type == cudaMemoryTypeManaged) return true;
+  return a.type == cudaMemoryTypeDevice && a.device == device;
+}
+}  // namespace
+
+extern "C" int neptune_rt_reduce_sum_static(const void *src, int dtype, int rank, const int64_t *shape, const int64_t *lb,
+                                            const int64_t *ub, double *result_dev, void *stream) {
+  if (!src || !shape || !result_dev) return set_error(nullptr, NEPTUNE_RT_EINVAL, "reduce_sum_static: NULL src, shape or result_dev");
+  if (dtype != NEPTUNE_RT_F32 && dtype != NEPTUNE_RT_F64)
+    return set_error(nullptr, NEPTUNE_RT_EINVAL, "reduce_sum_static: dtype %d is neither NEPTUNE_RT_F32 nor NEPTUNE_RT_F64", dtype);
+  if (rank < 1 || rank > NEPTUNE_RT_MAX_RANK)
+    return set_error(nullptr, NEPTUNE_RT_EINVAL, "reduce_sum_static: rank %d outside 1..%d", rank, NEPTUNE_RT_MAX_RANK);
+  int64_t zero[3] = {0, 0, 0}, flb[3], fext[3], blb[3], bext[3];
+  for (int d = 0; d < rank; ++d)
+    if (shape[d] < 0 || shape[d] > NEPTUNE_RT_REDUCE_STATIC_MAX_EXTENT)
+      return set_error(nullptr, NEPTUNE_RT_EINVAL,
+                       "reduce_sum_static: shape[%d] = %lld is beyond the limit of %lld elements per axis "
+                       "(NEPTUNE_RT_REDUCE_STATIC_MAX_EXTENT); split the axis or use neptune_rt_field_reduce_sum",
+                       d, (long long)shape[d], (long long)NEPTUNE_RT_REDUCE_STATIC_MAX_EXTENT);
+  canon_box(rank, zero, shape, flb, fext);
+  canon_box(rank, lb ? lb : zero, ub ? ub : shape, blb, bext);
+  bool empty = false;
+  for (int a = 0; a < 3; ++a) {
+    empty |= bext[a] <= 0;
+    if (bext[a] > 0 && (blb[a] < 0 || blb[a] + bext[a] > fext[a]))
+      return set_error(nullptr, NEPTUNE_RT_EINVAL, "reduce_sum_static: [lb, ub) leaves the array's shape");
+  }
+  int device = -1;
+  RT_CUDA(nullptr, cudaGetDevice(&device));
+  if (device < 0 || device >= STATIC_SCRATCH_MAX_DEVICES)
+    return set_error(nullptr, NEPTUNE_RT_EUNSUPPORTED, "reduce_sum_static: device ordinal %d outside 0..%d", device, STATIC_SCRATCH_MAX_DEVICES - 1);
+  if (!usable_on_device(src, device) || !usable_on_device(result_dev, device))
+    return set_error(nullptr, NEPTUNE_RT_EINVAL,
+                     "reduce_sum_static: src and result_dev must be device memory of the current device (%d); "
+                     "make the GPU that owns them current before the call", device);
+  if (((uintptr_t)result_dev & 7) != 0) return set_error(nullptr, NEPTUNE_RT_EINVAL, "reduce_sum_static: result_dev is not 8-byte aligned");
+  double *scratch = nullptr;
+  if (int rc = reduce_static_scratch(device, &scratch)) return rc;
+  cudaStream_t s = (cudaStream_t)stream;
+  if (empty) {
+    RT_CUDA(nullptr, cudaMemsetAsync(result_dev, 0, sizeof(double), s));   // +0.0, as the other entry point returns
+    return NEPTUNE_RT_OK;
+  }
+  const long long sy = fext[2], sz = fext[1] * fext[2];
+  const long long off = blb[0] * sz + blb[1] * sy + blb[2];
+  if (dtype == NEPTUNE_RT_F64)
+    reduce_sum_rows<double><<<REDUCE_BLOCKS, REDUCE_THREADS, 0, s>>>((const double *)src + off, sz, sy, (int)bext[0], (int)bext[1], (int)bext[2], scratch);
+  else
+    reduce_sum_rows<float><<<REDUCE_BLOCKS, REDUCE_THREADS, 0, s>>>((const float *)src + off, sz, sy, (int)bext[0], (int)bext[1], (int)bext[2], scratch);
+  RT_CUDA(nullptr, cudaGetLastError());
+  reduce_sum_final_static<<<1, REDUCE_THREADS, 0, s>>>(scratch, REDUCE_BLOCKS, result_dev, dtype == NEPTUNE_RT_F32);
+  RT_CUDA(nullptr, cudaGetLastError());
+  return NEPTUNE_RT_OK;
+}

@@ -89,6 +89,7 @@ def lib() -> C.CDLL:
         "neptune_rt_field_bytes": (i64, [vp]),
         "neptune_rt_field_store": (i32, [vp, vp, i64p, i64p]),
         "neptune_rt_field_reduce_sum": (i32, [vp, i64p, i64p, i32, C.POINTER(C.c_double)]),
+        "neptune_rt_reduce_sum_static": (i32, [vp, i32, i32, i64p, i64p, i64p, vp, vp]),
         "neptune_rt_body_key": (C.c_uint64, [C.POINTER(StencilDescC)]),
         "neptune_rt_body_compiled": (i32, [C.c_uint64]),
         "neptune_rt_body_jit_compile": (i32, [C.POINTER(StencilDescC), C.POINTER(C.c_double), C.c_char_p, C.c_size_t]),
