@@ -75,7 +75,24 @@ def program_for(kind, shape, ty, alpha, h2, lb=None):
     raise KeyError(kind)
 
 
-PARITY_STEPS = 4
+PARITY_STEPS = 4        # N = 1; in slab mode parity_steps_for() raises it until the plan holds exchanging launches
+
+
+def parity_steps_for(world, radius, ghost, fuse2):
+    """Time steps of the in-run parity check. One GPU: 4. Slabs: the smallest even count whose launch plan
+    (neptune_rt_slab_schedule — the function the time loop itself follows) contains at least TWO exchanging launches
+    and at least one non-exchanging launch after the last exchange, so that the split boundary/interior launches, the
+    halo push, the announce/join flags and a launch that consumes exchanged ghosts are all inside what is bit-compared."""
+    if world == 1:
+        return 4, None
+    from neptune_pde_solver_b200.runtime import slab_schedule
+    plan = None
+    for S in range(4, 49, 2):
+        plan = slab_schedule(S, radius, ghost, fuse2)
+        ex = [i for i, (_, _, x) in enumerate(plan) if x]
+        if len(ex) >= 2 and ex[-1] < len(plan) - 1:
+            return S, plan
+    return 48, plan
 
 
 class BandRows:
@@ -102,10 +119,11 @@ def band_row_ranges(world, own_rows):
 
 def band_parity_check(kind, ty, alpha, h2, world, rank, own_rows, u_local, extra_local, run_fn, gather_fn):
     """Bitwise parity inside the benchmark run, on the ACTUAL configuration (kernel variant, slab decomposition,
-    ghost depth, NCCL exchange): 4 steps from the benchmark's initial state, then an 8-plane band that straddles
+    ghost depth, halo exchange): S = PARITY_STEPS steps from the benchmark's initial state (4 on one GPU; in slab mode
+    as many as the launch plan needs to hold two exchanges, see parity_steps_for), then a 2S-plane band that straddles
     every slab boundary (N = 1: the middle of the domain) is compared with the oracle run on the band's dependency
-    cone (16 planes x a corner block that includes two real faces; the cone's own cut faces cannot reach the band
-    in 4 steps).  The oracle is the checker here, never the thing measured."""
+    cone (4S planes x a corner block that includes two real faces; the cone's own cut faces cannot reach the band
+    in S steps).  The oracle is the checker here, never the thing measured."""
     rank_nd = u_local.ndim
     cut = (slice(0, min(96, u_local.shape[1])), slice(0, min(160, u_local.shape[2]))) if rank_nd == 3 else (slice(0, min(4096, u_local.shape[1])),)
     ob, oe = own_rows
@@ -142,7 +160,7 @@ def band_parity_check(kind, ty, alpha, h2, world, rank, own_rows, u_local, extra
         ok &= eq
         bands.append({"band": pk["where"], "points": int(a.size), "bits_equal": eq})
     return {"bits_equal": ok, "steps": S, "bands": bands,
-            "oracle": "oracle/numpy_lowering.py on each band's 16-plane dependency cone (restatement of DataflowLowering.cpp:258-448)"}
+            "oracle": "oracle/numpy_lowering.py on each band's %d-plane dependency cone (restatement of DataflowLowering.cpp:258-448)" % (4 * S)}
 
 
 def synth(shape, ty, seed):
@@ -283,7 +301,7 @@ def run_reference(args):
     shape = WORKLOADS[args.workload][1]
     # each "step" = one faithful sweep; K + W bounded so the run ends within a few minutes
     k = max(1, min(args.steps, 20))
-    w = max(0, min(args.warmup, 2))
+    w = max(0, args.warmup)     # as asked (a 512^3 sweep on one core takes about 0.8 s, so even W = 10 stays within seconds)
     gups, ms, n, cores = cpu_reference_arm(args.workload, shape, budget_s=1e9, min_steps=k, max_steps=k, warmup=w)
     line = {
         "impl": "reference", "metric": METRIC, "value": gups, "unit": UNIT, "n_gpus": args.gpus,
@@ -379,6 +397,13 @@ def run_b200(args):
     if args.zchunk and args.zchunk != "0":
         stencil.set("zchunk", args.zchunk)
 
+    global PARITY_STEPS
+    parity_plan = None
+    if world > 1 and not args.no_parity:
+        PARITY_STEPS, parity_plan = parity_steps_for(world, gdesc.radius0(), slab.halo, bool(fusable))
+        if slab.own_rows[1] - slab.own_rows[0] < 2 * PARITY_STEPS:
+            raise SystemExit("bench.py: slabs of %d planes are too thin for a %d-step parity band" % (slab.own_rows[1] - slab.own_rows[0], PARITY_STEPS))
+
     u = synth(lshape, ty, 20260403 + rank)
     fa = nb.Field(ctx, dt, lb, ub)
     fb = nb.Field(ctx, dt, lb, ub)
@@ -415,8 +440,15 @@ def run_b200(args):
         else:
             ob, oe = 0, lshape[0]
 
+        traced = []
+
         def run_fn(nsteps):
+            if world > 1:
+                ctx.slab_trace(True)
             r = stencil.run_steps(fa, fb, extra, nsteps)
+            if world > 1:
+                traced.extend(g[0] for g in ctx.slab_trace_read())    # 10 * steps advanced + (1 if the launch exchanged)
+                ctx.slab_trace(False)
             return r.download()
 
         def gather_fn(mine):
@@ -431,6 +463,22 @@ def run_b200(args):
             ok = flag[0]
         else:
             ok = parity["bits_equal"]
+        if world > 1:
+            # the launches the checked run REALLY made (slab trace of this rank), beside the plan they were predicted from
+            executed = [[k // 10, k % 10] for k in traced]
+            n_ex = sum(1 for k in traced if k % 10)
+            cnt = [None] * world
+            dist.all_gather_object(cnt, n_ex)
+            if rank == 0:
+                parity["plan"] = {"columns": ["steps", "exchange", "ghost planes computed redundantly"],
+                                  "predicted": [[st, int(x), ext] for (st, ext, x) in (parity_plan or [])],
+                                  "executed_on_rank0": executed, "exchanging_launches_per_rank": cnt,
+                                  "halo_mode": stencil.halo_mode()}
+            if min(cnt) < 2:
+                ok = False
+                if rank == 0:
+                    parity["bits_equal"] = False
+                    parity["error"] = "the checked run made fewer than two exchanging launches: the exchange path is not covered"
         if rank == 0:
             parity["kernel_variant"] = stencil.variant()
         if not ok:
@@ -478,6 +526,33 @@ def run_b200(args):
     ms_per_step = ms_max / args.steps
     value = total_points / (ms_per_step * 1e-3) / 1e9
     variant = stencil.variant()
+
+    # ---- sustained: the same loop for >= --sustained-seconds in one go, with its own clock samples. `value` above is a
+    # burst figure (K steps last a few ms at K = 20: the GPU has not reached its power limit yet); under sw_power_cap the
+    # clocks settle lower and this is the number a long run sees ------------------------------------------------------
+    sustained = None
+    if args.sustained_seconds > 0:
+        n_s = max(args.steps, int(np.ceil(args.sustained_seconds * 1e3 / ms_per_step)))
+        n_s += n_s % 2
+        sampler2 = ClockSampler(local)
+        barrier()
+        if rank == 0:
+            sampler2.start()
+        t_s0 = time.time()
+        ctx.timer_start()
+        cur = stencil.run_steps(cur, other, extra, n_s)
+        ms_s = ctx.timer_stop()
+        other = fb if cur is fa else fa
+        barrier()
+        t_s1 = time.time()
+        if world > 1:
+            t = torch.tensor([ms_s], dtype=torch.float64, device="cuda")
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms_s = float(t[0])
+        sustained = {"value": total_points / (ms_s / n_s * 1e-3) / 1e9, "unit": UNIT, "steps": n_s, "seconds": ms_s * 1e-3,
+                     "ms_per_step": ms_s / n_s, "clocks": sampler2.stop(t_s0, t_s1) if rank == 0 else None,
+                     "note": "one uninterrupted run of the timed loop, CUDA events on the sweep stream, max over ranks; "
+                             "`value` is the burst figure of the K-step repetitions"}
 
     # ---- timeline of the slab time loop (one rank with two neighbours where there is one) ----------
     slab_trace = None
@@ -671,7 +746,7 @@ def run_b200(args):
                        "parity_check": parity,
                        "l2": "inputs larger than L2 (%.2f GB per field vs 126 MB L2); no flush needed" % (field_bytes / 1e9),
                        "fma": False},
-            "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e,
+            "sustained": sustained, "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e,
             "gpu_launches": int(launches_all), "e2e_gpu_launches": int(e_launches), "clocks": clocks,
             "achieved_GBps_step": total_points * bytes_per_update / (ms_per_step * 1e-3) / 1e9 / world,
         }
@@ -696,8 +771,9 @@ def main():
     ap.add_argument("--variant", default="")
     ap.add_argument("--zchunk", default="")
     ap.add_argument("--tblock", type=int, default=0, help="temporal block depth: 1 or 2 steps per launch (0 = library default); 4 / 8 = two steps per launch and, in slab mode, one exchange of tblock * radius ghost planes per tblock steps")
-    ap.add_argument("--ghost", type=int, default=0, help="ghost planes per neighbour side in slab mode (0 = 2 * radius where two steps fuse, else radius)")
+    ap.add_argument("--ghost", type=int, default=0, help="ghost planes per neighbour side in slab mode (0 = 4 * radius where two steps fuse [--tblock d >= 2: d * radius], else radius)")
     ap.add_argument("--reps", type=int, default=5, help="repetitions of the K-step timed region; the median is reported")
+    ap.add_argument("--sustained-seconds", type=float, default=2.0, help="length of the additional uninterrupted run reported as `sustained` (0 = skip)")
     ap.add_argument("--no-parity", action="store_true", help="skip the in-run bitwise parity check against the oracle")
     ap.add_argument("--trace", action="store_true", help="N > 1: add per-launch-group timestamps of the slab time loop")
     ap.add_argument("--link-probe", action="store_true", help="add a bare pinned-memcpy H2D+D2H measurement (all ranks at once) to e2e")

@@ -18,6 +18,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <ctime>
 #include <functional>
 #include <initializer_list>
 #include <memory>
@@ -120,6 +121,7 @@ struct neptune_rt_ctx {
   cudaStream_t h2d_stream = nullptr, d2h_stream = nullptr;  // copy engines of the pipelined host path
   std::vector<cudaEvent_t> ev_pool;                          // per-chunk events of neptune_rt_apply_host
   int64_t launches = 0;
+  uint64_t next_field_id = 1;   // fields are numbered in creation order: the same numbers on every rank of an SPMD program
   std::string err;
   ncclComm_t comm = nullptr;
   int nranks = 1, rank = 0;
@@ -139,7 +141,17 @@ struct neptune_rt_ctx {
   // NVLink (cudaMemcpyAsync into CUDA-IPC-mapped memory) and ordered with stream memory operations on four flag words
   // per rank, so that no kernel — and therefore no SM — takes part in the exchange
   bool p2p = false;
-  uint32_t *flags = nullptr;                       // [0] READY from up, [1] READY from down, [2] ARRIVED from up, [3] ARRIVED from down
+  uint32_t *flags = nullptr;                       // [0] READY from up, [1] READY from down, [2] ARRIVED from up, [3] ARRIVED from down,
+                                                   // [4] / [5] how many of my exported fields the up / down neighbour has unmapped (a
+                                                   // watermark, see ipc_release_field), [6] / [7] that neighbour has unmapped these flags
+  // Teardown of IPC-exported memory: an allocation a neighbour still maps must not be cudaFree'd. Exports towards each
+  // side are numbered in the order they are made (the same numbers on both ends of the pair); the importer reports
+  // "everything up to n is unmapped" into the exporter's flag words, and an allocation whose number is above that
+  // waits in `deferred` (looked at again at every later free, and at finalize with a bounded wait). No collective.
+  uint32_t ipc_seq[2] = {0, 0};                    // last export/import number handed out towards up / down
+  std::set<uint32_t> ipc_open[2];                  // import numbers (of the up / down neighbour's fields) I still map
+  struct DeferredFree { void *ptr; uint32_t need[2]; };
+  std::vector<DeferredFree> deferred;
   uint32_t *peer_flags[2] = {nullptr, nullptr};    // the up / down neighbour's flag words (IPC-mapped)
   uint32_t epoch = 0;                              // exchanges so far (the same on every rank: SPMD)
   unsigned wait_flags = 0;
@@ -155,10 +167,12 @@ struct neptune_rt_field {
   void *dptr = nullptr;
   size_t bytes = 0;
   bool owned = true;   // false: caller's device memory (neptune_rt_field_wrap_device)
-  // peer-to-peer halo path: the up / down neighbour's corresponding field, IPC-mapped, and where my boundary planes land in it
+  // peer-to-peer halo path: the up / down neighbour's corresponding field, IPC-mapped (where my boundary planes land in
+  // it depends on the ghost depth, so that is kept with the stencil's agreement, not here)
   bool peer_mapped = false;
   void *peer_base[2] = {nullptr, nullptr};
-  size_t peer_off[2] = {0, 0};
+  uint32_t ipc_seq[2] = {0, 0};   // this field's export number towards the up / down neighbour (0: never exported there)
+  uint64_t id = 0;     // never reused, unlike the address: what the slab agreement cache is keyed on
   size_t elsize() const { return dtype == NEPTUNE_RT_F64 ? 8 : 4; }
   int64_t numel() const { return ext[0] * ext[1] * ext[2]; }
 };
@@ -188,12 +202,18 @@ struct neptune_rt_stencil {
   std::vector<TmapEntry> tmaps;
   bool slab_loop = false;   // set by neptune_rt_run_steps around its slab launches: dim-0 bounds are the GLOBAL ones
   // what the ranks agreed for the last (fields, settings) neptune_rt_run_steps saw in slab mode
+  // Keyed on field ids (creation order, identical on every rank, never reused) and on every setting that feeds the
+  // decision, so that all ranks hit or miss together: a miss is a collective (neighbour swaps + an all-reduce).
+  // neptune_rt_stencil_set / _set_slab also drop it.
   struct Agreed {
     bool valid = false, fuse2 = false, split = false, p2p = false;
-    neptune_rt_field *a = nullptr, *b = nullptr;
-    std::vector<neptune_rt_field *> extra;
+    uint64_t a = 0, b = 0;
+    std::vector<uint64_t> extra;
     int tblock = 0;
+    int64_t ghost = 0, glb0 = 0, gub0 = 0;
     std::string want_tb;
+    // p2p: byte offsets of my boundary planes inside the up / down neighbour's copy of field a / b, for THIS ghost depth
+    size_t peer_off[2][2] = {{0, 0}, {0, 0}};
   } agreed;
 };
 
@@ -382,6 +402,57 @@ extern "C" int neptune_rt_timer_stop(neptune_rt_ctx *c, double *ms) {
   return NEPTUNE_RT_OK;
 }
 
+namespace {
+// How far each neighbour has got in unmapping my exports (flag words 4 and 5, written by the neighbours).
+void ipc_read_watermarks(neptune_rt_ctx *c, uint32_t wm[2]) {
+  wm[0] = wm[1] = 0;
+  if (c->flags && cudaMemcpy(wm, c->flags + 4, 2 * sizeof(uint32_t), cudaMemcpyDeviceToHost) != cudaSuccess) cudaGetLastError();
+}
+// cudaFree what no neighbour maps any more; with wait_ms > 0 poll that long for the rest, then (force) free it anyway.
+void ipc_drain_deferred(neptune_rt_ctx *c, int wait_ms, bool force) {
+  for (int waited = 0;; ++waited) {
+    if (c->deferred.empty()) return;
+    uint32_t wm[2];
+    ipc_read_watermarks(c, wm);
+    for (size_t i = 0; i < c->deferred.size();) {
+      if (wm[0] >= c->deferred[i].need[0] && wm[1] >= c->deferred[i].need[1]) {
+        cudaFree(c->deferred[i].ptr);
+        c->deferred.erase(c->deferred.begin() + (long)i);
+      } else {
+        ++i;
+      }
+    }
+    if (c->deferred.empty() || waited >= wait_ms) break;
+    struct timespec ts = {0, 1000000};
+    nanosleep(&ts, nullptr);
+  }
+  if (force) {
+    for (auto &d : c->deferred) cudaFree(d.ptr);
+    c->deferred.clear();
+  }
+}
+// A field is going away: unmap the neighbours' copies, tell each neighbour how far my unmapping has got, and free my
+// own allocation now if no neighbour maps it, later otherwise.
+void ipc_release_field(neptune_rt_ctx *c, neptune_rt_field *f) {
+  for (int side = 0; side < 2; ++side) {
+    if (!f->peer_base[side]) continue;
+    cudaIpcCloseMemHandle(f->peer_base[side]);
+    f->peer_base[side] = nullptr;
+    c->ipc_open[side].erase(f->ipc_seq[side]);
+    // everything below the lowest number I still map is unmapped (numbers whose open failed never entered the set)
+    const uint32_t wm = c->ipc_open[side].empty() ? c->ipc_seq[side] : *c->ipc_open[side].begin() - 1;
+    // I am the up neighbour's DOWN neighbour (its word 5) and the down neighbour's UP neighbour (its word 4)
+    if (c->peer_flags[side] && cudaMemcpy(c->peer_flags[side] + (side == 0 ? 5 : 4), &wm, sizeof wm, cudaMemcpyHostToDevice) != cudaSuccess)
+      cudaGetLastError();
+  }
+  if (f->owned && f->dptr) {
+    if (f->ipc_seq[0] || f->ipc_seq[1]) c->deferred.push_back({f->dptr, {f->ipc_seq[0], f->ipc_seq[1]}});
+    else cudaFree(f->dptr);
+  }
+  ipc_drain_deferred(c, 0, false);
+}
+}  // namespace
+
 extern "C" int neptune_rt_finalize(neptune_rt_ctx *c) {
   if (!c) return NEPTUNE_RT_OK;
   cudaSetDevice(c->device);
@@ -400,9 +471,27 @@ extern "C" int neptune_rt_finalize(neptune_rt_ctx *c) {
   for (cudaEvent_t e : c->trace_events) cudaEventDestroy(e);
   if (c->red_partials) cudaFree(c->red_partials);
   if (c->red_host) cudaFreeHost(c->red_host);
-  for (uint32_t *pf : c->peer_flags)
-    if (pf) cudaIpcCloseMemHandle(pf);
-  if (c->flags) cudaFree(c->flags);
+  // exported memory goes last: first what the neighbours have already unmapped, then (after at most a second of
+  // waiting for ranks that are a little behind in their own teardown) the rest; the flag words themselves the same way
+  ipc_drain_deferred(c, 1000, true);
+  for (int side = 0; side < 2; ++side)
+    if (c->peer_flags[side]) {
+      const uint32_t one = 1;   // my last write through this mapping: "I have unmapped your flags" (its word 7 / 6)
+      if (cudaMemcpy(c->peer_flags[side] + (side == 0 ? 7 : 6), &one, sizeof one, cudaMemcpyHostToDevice) != cudaSuccess) cudaGetLastError();
+      cudaIpcCloseMemHandle(c->peer_flags[side]);
+      c->peer_flags[side] = nullptr;
+    }
+  if (c->flags) {
+    const bool expect[2] = {c->p2p && c->rank > 0, c->p2p && c->rank + 1 < c->nranks};
+    for (int waited = 0; waited < 1000; ++waited) {
+      uint32_t gone[2] = {0, 0};
+      if (cudaMemcpy(gone, c->flags + 6, sizeof gone, cudaMemcpyDeviceToHost) != cudaSuccess) { cudaGetLastError(); break; }
+      if ((!expect[0] || gone[0]) && (!expect[1] || gone[1])) break;
+      struct timespec ts = {0, 1000000};
+      nanosleep(&ts, nullptr);
+    }
+    cudaFree(c->flags);
+  }
   if (c->agree_dev) cudaFree(c->agree_dev);
   if (c->agree_host) cudaFreeHost(c->agree_host);
   for (auto &fn : c->on_finalize) fn();
@@ -451,6 +540,7 @@ extern "C" int neptune_rt_field_alloc(neptune_rt_ctx *c, int dtype, int rank, co
     return set_error(c, e == cudaErrorMemoryAllocation ? NEPTUNE_RT_ENOMEM : NEPTUNE_RT_ECUDA,
                      "cudaMalloc of a %zu-byte field failed: %s", (size_t)0 + f->bytes, cudaGetErrorString(e));
   }
+  f->id = c->next_field_id++;
   c->live_fields.insert(f);
   *out = f;
   return NEPTUNE_RT_OK;
@@ -463,9 +553,7 @@ extern "C" int neptune_rt_field_free(neptune_rt_field *f) {
   // the halo, upload and download streams may still be reading or writing this field
   for (cudaStream_t st : {f->ctx->halo_stream, f->ctx->h2d_stream, f->ctx->stream, f->ctx->d2h_stream})
     if (st) cudaStreamSynchronize(st);
-  for (void *pb : f->peer_base)
-    if (pb) cudaIpcCloseMemHandle(pb);
-  if (f->owned) cudaFree(f->dptr);
+  ipc_release_field(f->ctx, f);   // unmaps the neighbours' copies; cudaFree now, or once no neighbour maps this allocation
   delete f;
   return NEPTUNE_RT_OK;
 }
@@ -496,6 +584,7 @@ extern "C" int neptune_rt_field_wrap_device(neptune_rt_ctx *c, int dtype, int ra
   canon_box(rank, lb, ub, clb, f->ext);
   f->bytes = (size_t)f->numel() * f->elsize();
   f->dptr = device_ptr;
+  f->id = c->next_field_id++;
   c->live_fields.insert(f);
   *out = f;
   return NEPTUNE_RT_OK;
@@ -695,6 +784,7 @@ extern "C" int neptune_rt_stencil_destroy(neptune_rt_stencil *s) {
 extern "C" int neptune_rt_stencil_set(neptune_rt_stencil *s, const char *key, const char *value) {
   if (!s || !key || !value) return set_error(s ? s->ctx : nullptr, NEPTUNE_RT_EINVAL, "stencil_set: NULL argument");
   const std::string k = key, v = value;
+  s->agreed.valid = false;   // any setting may change what the ranks have to agree on; they all set it (SPMD)
   if (k == "variant" && v.rfind("tb2", 0) == 0) {
     bool found = false;
     for (auto &var : s->body->variants) found |= var.name == v && var.kind == neptune::VARIANT_TB2;
@@ -911,7 +1001,6 @@ int do_apply(neptune_rt_stencil *s, int n_in, neptune_rt_field *const *in, neptu
       // r02: tb2q:128x14 (tb2p's data movement with a lean steady state, conflict-free ring pitches) 541+ Gupd/s
       const bool deep = (p1 - p0) - (g1 - g0) >= 24 && !gap;
       const char *prefer[] = {n_in > 1 ? two_in : wide ? (deep ? "tb2q:128x14" : "tb2m:128x14") : "tb2:64x16",
-                              wide && deep ? "tb2p:128x14" : wide ? "tb2m:128x14" : "tb2:64x16",
                               wide ? "tb2m:128x14" : "tb2:64x16"};
       for (const char *name : prefer) {
         for (auto &v : s->body->variants)
@@ -1243,7 +1332,7 @@ void p2p_setup(neptune_rt_ctx *c) {
 }
 
 // the neighbours' copies of `f`, mapped into this process, and where this rank's boundary planes land in them
-int p2p_map_field(neptune_rt_ctx *c, neptune_rt_field *f, int64_t own_b, int64_t own_e, int64_t ghost, bool *ok_out) {
+int p2p_map_field(neptune_rt_ctx *c, neptune_rt_field *f, int64_t own_b, int64_t own_e, int64_t ghost, bool *ok_out, size_t off_out[2]) {
   const int cd0 = 3 - f->rank;
   const size_t plane = f->ext[cd0] ? f->bytes / (size_t)f->ext[cd0] : 0;
   bool ok = f->owned;                               // wrapped memory may sit inside another allocation: not exportable as it is
@@ -1259,6 +1348,7 @@ int p2p_map_field(neptune_rt_ctx *c, neptune_rt_field *f, int64_t own_b, int64_t
   std::memcpy(tx_down + 8, &mine, sizeof mine); std::memcpy(tx_down + 8 + sizeof mine, &off_from_down, 8);
   if (int rc = neighbour_swap(c, tx_up, rx_up, tx_down, rx_down, 128)) return rc;
   const bool up = c->rank > 0, down = c->rank + 1 < c->nranks;
+  const bool exportable = ok;   // what the neighbours were told
   for (int side = 0; side < 2; ++side) {
     if (!(side == 0 ? up : down)) continue;
     const char *rx = side == 0 ? rx_up : rx_down;
@@ -1266,12 +1356,16 @@ int p2p_map_field(neptune_rt_ctx *c, neptune_rt_field *f, int64_t own_b, int64_t
     std::memcpy(&h, rx + 8, sizeof h);
     uint64_t off = 0;
     std::memcpy(&off, rx + 8 + sizeof h, 8);
+    // numbering: decided from the two swapped flags alone (never from a local failure), so both ends of the pair count
+    // alike: the neighbour's export number for the field I am about to map is mine for the one it maps
+    if (exportable && rx[0] == 1 && !f->ipc_seq[side]) f->ipc_seq[side] = ++c->ipc_seq[side];
     if (ok && rx[0] == 1 && !f->peer_base[side]) {
       if (cudaIpcOpenMemHandle(&f->peer_base[side], h, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) { f->peer_base[side] = nullptr; ok = false; cudaGetLastError(); }
+      else c->ipc_open[side].insert(f->ipc_seq[side]);
     } else if (rx[0] != 1) {
       ok = false;
     }
-    f->peer_off[side] = (size_t)off;
+    off_out[side] = (size_t)off;
   }
   f->peer_mapped = ok;
   *ok_out = ok;
@@ -1293,7 +1387,7 @@ int p2p_announce(neptune_rt_ctx *c, uint32_t e) {
     return set_error(c, NEPTUNE_RT_ECUDA, "cuStreamWriteValue32 (halo announce) failed");
   return NEPTUNE_RT_OK;
 }
-int p2p_push(neptune_rt_ctx *c, neptune_rt_field *f, int64_t own_b, int64_t own_e, int64_t w, uint32_t e) {
+int p2p_push(neptune_rt_ctx *c, neptune_rt_field *f, const size_t peer_off[2], int64_t own_b, int64_t own_e, int64_t w, uint32_t e) {
   const bool up = c->rank > 0, down = c->rank + 1 < c->nranks;
   const int cd0 = 3 - f->rank;
   const size_t plane = f->ext[cd0] ? f->bytes / (size_t)f->ext[cd0] : 0, n = plane * (size_t)w;
@@ -1301,12 +1395,12 @@ int p2p_push(neptune_rt_ctx *c, neptune_rt_field *f, int64_t own_b, int64_t own_
   CUstream H = (CUstream)c->halo_stream;
   if (up) {
     if (c->StreamWaitValue32(H, (CUdeviceptr)(c->flags + 0), e, c->wait_flags) != CUDA_SUCCESS) return set_error(c, NEPTUNE_RT_ECUDA, "cuStreamWaitValue32 (halo push) failed");
-    RT_CUDA(c, cudaMemcpyAsync((char *)f->peer_base[0] + f->peer_off[0], base + (size_t)own_b * plane, n, cudaMemcpyDeviceToDevice, c->halo_stream));
+    RT_CUDA(c, cudaMemcpyAsync((char *)f->peer_base[0] + peer_off[0], base + (size_t)own_b * plane, n, cudaMemcpyDeviceToDevice, c->halo_stream));
     if (c->StreamWriteValue32(H, (CUdeviceptr)(c->peer_flags[0] + 3), e, CU_STREAM_WRITE_VALUE_DEFAULT) != CUDA_SUCCESS) return set_error(c, NEPTUNE_RT_ECUDA, "cuStreamWriteValue32 (halo arrived) failed");
   }
   if (down) {
     if (c->StreamWaitValue32(H, (CUdeviceptr)(c->flags + 1), e, c->wait_flags) != CUDA_SUCCESS) return set_error(c, NEPTUNE_RT_ECUDA, "cuStreamWaitValue32 (halo push) failed");
-    RT_CUDA(c, cudaMemcpyAsync((char *)f->peer_base[1] + f->peer_off[1], base + (size_t)(own_e - w) * plane, n, cudaMemcpyDeviceToDevice, c->halo_stream));
+    RT_CUDA(c, cudaMemcpyAsync((char *)f->peer_base[1] + peer_off[1], base + (size_t)(own_e - w) * plane, n, cudaMemcpyDeviceToDevice, c->halo_stream));
     if (c->StreamWriteValue32(H, (CUdeviceptr)(c->peer_flags[1] + 2), e, CU_STREAM_WRITE_VALUE_DEFAULT) != CUDA_SUCCESS) return set_error(c, NEPTUNE_RT_ECUDA, "cuStreamWriteValue32 (halo arrived) failed");
   }
   return NEPTUNE_RT_OK;
@@ -1436,8 +1530,9 @@ extern "C" int neptune_rt_run_steps(neptune_rt_stencil *s, neptune_rt_field *fa,
   {
     neptune_rt_stencil::Agreed &ag = s->agreed;
     bool same = ag.valid && ag.tblock == s->tblock && ag.want_tb == s->want_tb && (int)ag.extra.size() == n_extra &&
-                ((ag.a == fa && ag.b == fb) || (ag.a == fb && ag.b == fa));
-    for (int k = 0; same && k < n_extra; ++k) same = ag.extra[(size_t)k] == extra[k];
+                ag.ghost == ghost && ag.glb0 == s->slab_glb0 && ag.gub0 == s->slab_gub0 &&
+                ((ag.a == fa->id && ag.b == fb->id) || (ag.a == fb->id && ag.b == fa->id));
+    for (int k = 0; same && k < n_extra; ++k) same = ag.extra[(size_t)k] == extra[k]->id;
     if (!same) {
       int local[4];
       local[0] = (s->tblock != 1 && ghost >= 2 * radius && own_e - own_b >= 4 * radius && tb2_eligible(s, cur, nxt, true, n_extra, extra)) ? 1 : 0;
@@ -1452,9 +1547,11 @@ extern "C" int neptune_rt_run_steps(neptune_rt_stencil *s, neptune_rt_field *fa,
         if (!(mode && std::strcmp(mode, "nccl") == 0)) {
           std::vector<neptune_rt_field *> fs = {fa, fb};
           for (int k = 0; k < n_extra; ++k) fs.push_back(extra[k]);
-          for (neptune_rt_field *f : fs) {
+          for (size_t i = 0; i < fs.size(); ++i) {
             bool ok = false;
-            if (int rc = p2p_map_field(c, f, own_b, own_e, ghost, &ok)) return rc;
+            size_t off[2] = {0, 0};
+            if (int rc = p2p_map_field(c, fs[i], own_b, own_e, ghost, &ok, off)) return rc;
+            if (i < 2) { ag.peer_off[i][0] = off[0]; ag.peer_off[i][1] = off[1]; }   // only the state fields are pushed
             p2p_ok = p2p_ok && ok;
           }
         } else {
@@ -1478,8 +1575,10 @@ extern "C" int neptune_rt_run_steps(neptune_rt_stencil *s, neptune_rt_field *fa,
       ag.fuse2 = c->agree_host[0] != 0;
       ag.split = c->agree_host[1] != 0;
       ag.p2p = c->agree_host[3] != 0;
-      ag.a = fa; ag.b = fb;
-      ag.extra.assign(extra, extra + n_extra);
+      ag.a = fa->id; ag.b = fb->id;
+      ag.extra.clear();
+      for (int k = 0; k < n_extra; ++k) ag.extra.push_back(extra[k]->id);
+      ag.ghost = ghost; ag.glb0 = s->slab_glb0; ag.gub0 = s->slab_gub0;
       ag.tblock = s->tblock;
       ag.want_tb = s->want_tb;
     }
@@ -1528,7 +1627,7 @@ extern "C" int neptune_rt_run_steps(neptune_rt_stencil *s, neptune_rt_field *fa,
     RT_CUDA(c, cudaEventRecord(c->ev_boundary, c->stream));
     RT_CUDA(c, cudaStreamWaitEvent(c->halo_stream, c->ev_boundary, 0));
     if (p2p) {
-      if (int rc = p2p_push(c, f, own_b, own_e, ghost, ex_epoch)) return rc;
+      if (int rc = p2p_push(c, f, s->agreed.peer_off[f->id == s->agreed.a ? 0 : 1], own_b, own_e, ghost, ex_epoch)) return rc;
     } else {
       if (int rc = neptune_rt_halo_exchange(c, f, own_b, own_e, ghost, c->halo_stream)) return rc;
     }
@@ -1637,6 +1736,7 @@ extern "C" int neptune_rt_stencil_set_slab(neptune_rt_stencil *s, int64_t ghost,
   s->slab_ghost = ghost;
   s->slab_glb0 = global_lb0;
   s->slab_gub0 = global_ub0;
+  s->agreed.valid = false;   // ghost depth and global bounds feed the agreement (every rank calls this: SPMD)
   return NEPTUNE_RT_OK;
 }
 

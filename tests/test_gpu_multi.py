@@ -192,3 +192,91 @@ def test_slab_loop_reports_its_exchange_mode_and_timeline():
     assert mode == ("nccl" if os.environ.get("NEPTUNE_RT_HALO") == "nccl" else "p2p")   # GPUs of one node: copy engines + flags
     assert kinds == planned          # the loop followed neptune_rt_slab_schedule: [20, 21, 20, 20] for 8 steps, 4 ghost planes
     assert ordered
+
+
+def _worker_realloc(rank, world, port, q, cycles):
+    import torch
+    import torch.distributed as dist
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    torch.cuda.set_device(rank)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        import neptune_pde_solver_b200 as nb
+        from neptune_pde_solver_b200.slab import Slab
+        shape, steps, halo = (64, 48, 64), 10, 4
+        gtext, _ = H.program("heat_star", list(shape), "f64")
+        g = nb.Module(gtext).apply_desc(0)
+        s = Slab(g, world, rank, halo)
+        ctx = nb.Context(rank)
+        uid = [nb.comm_unique_id() if rank == 0 else None]
+        dist.broadcast_object_list(uid, src=0)
+        ctx.comm_init(uid[0], world, rank)
+        st = s.stencil(ctx)
+        lb, ub = s.local.out_lb, s.local.out_ub
+        free0 = 0
+        ok, modes, ptrs = True, set(), set()
+        for cyc in range(cycles):
+            u, _ = H.inputs(shape, 0, "f64", seed=500 + cyc)
+            fa, fb = nb.Field(ctx, np.float64, lb, ub), nb.Field(ctx, np.float64, lb, ub)
+            ptrs.update((fa.device_ptr(), fb.device_ptr()))
+            loc = s.scatter(u)
+            fa.upload(loc)
+            fb.upload(loc)
+            if cyc % 5 == 4:
+                st.set_slab(halo, g.lb[0], g.ub[0])       # same values: the agreement is dropped and made again
+            res = st.run_steps(fa, fb, [], steps)
+            modes.add(st.halo_mode())
+            got = s.owned(res.download()).copy()
+            parts = [None] * world
+            dist.all_gather_object(parts, (s.begin, got))
+            if rank == 0:
+                full = np.concatenate([p[1] for p in sorted(parts, key=lambda p: p[0])], axis=0)
+                ok = ok and bool(H.bits_equal(full, H.oracle_steps(gtext, u, [], steps)))
+            # freed while the neighbours may still map them; rank 1 lags behind on purpose, so that its neighbours
+            # free (and re-allocate) before it has unmapped their fields
+            if rank == 1:
+                import time
+                time.sleep(0.02)
+            fb.free()
+            fa.free()
+            if cyc == 1:
+                # baseline after two whole cycles: by now NCCL's channel buffers and the CUDA modules are resident
+                dist.barrier()
+                ctx.sync()
+                free0 = torch.cuda.mem_get_info(rank)[0]
+        dist.barrier()
+        ctx.sync()
+        leaked = free0 - torch.cuda.mem_get_info(rank)[0]
+        if rank == 0:
+            q.put((ok, sorted(modes), len(ptrs), leaked))
+        ctx.close()
+    finally:
+        dist.destroy_process_group()
+
+
+def test_fields_freed_and_reallocated_between_slab_runs():
+    """20 cycles of allocate -> run the slab loop (p2p: the neighbours IPC-map the fields) -> free, with one rank
+    lagging: every cycle bit-equal to the single-domain oracle, although device addresses are reused by later
+    fields (the agreement cache is keyed on field ids, not addresses) and the agreement is dropped by set_slab
+    every fifth cycle.  Exported allocations are released only once the neighbours have unmapped them
+    (ipc_release_field in runtime.cu), and in the end nothing stays allocated."""
+    import torch
+    import torch.multiprocessing as mp
+    ngpu = torch.cuda.device_count()
+    if ngpu < 2:
+        pytest.skip("needs >= 2 GPUs")
+    world = min(ngpu, 4)
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_worker_realloc, args=(r, world, port, q, 20)) for r in range(world)]
+    for p in procs:
+        p.start()
+    for p in procs:
+        p.join(300)
+        assert p.exitcode == 0
+    ok, modes, distinct, leaked = q.get(timeout=5)
+    assert ok is True
+    assert modes in (["p2p"], ["nccl"])
+    assert 2 <= distinct <= 40                 # (how many distinct addresses the 40 fields of rank 0 had: usually a handful)
+    assert leaked <= 32 << 20, leaked          # 18 further cycles left nothing behind: deferred frees were released
