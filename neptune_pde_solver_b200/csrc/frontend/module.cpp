@@ -480,6 +480,7 @@ extern "C" int neptune_b200_compile(const char *text, const char *pipeline, nept
             recs.push_back(std::move(r));
           }
       } catch (const Diagnostic &d) {
+        if (!d.unsupported) throw;   // invalid IR (e.g. the linear-region rule): the whole module fails, as in the reference
         reject(fn, d);
         continue;
       }
@@ -510,6 +511,9 @@ extern "C" int neptune_b200_compile(const char *text, const char *pipeline, nept
         analyze_function(*m, fn, m->fns[fn.name]);
         ++lowered;
       } catch (const Diagnostic &d) {
+        // a broken rule (the linear-region rule, a bounds mismatch ...) is an invalid module, not an unsupported one:
+        // the reference's VerifyAndAnnotate fails the pass and with it the whole module
+        if (!d.unsupported) throw;
         m->fns.erase(fn.name);
         reject(fn, d);
       }

@@ -426,7 +426,7 @@ class Parser {
   }
 
   // The operations of a function up to its closing brace.  A function that holds something outside the hot path
-  // (neptune_ir.time_advance, solve_linear, a body with control flow ...) or that breaks a verifier rule is kept
+  // (neptune_ir.time_advance, solve_linear, a body with control flow ...) is kept
   // as a REJECTED function carrying the diagnostic, and parsing resumes after its closing brace: the other
   // functions of the module — the operator definitions a time_advance refers to, for one — are still lowered.
   // (The reference's conversion fails the whole module; a module none of whose functions lowers still fails here.)
@@ -435,6 +435,9 @@ class Parser {
     try {
       while (!accept("}")) fn.ops.push_back(parse_host_op());
     } catch (const Diagnostic &d) {
+      // only IR that is well formed but off the hot path is set aside; a syntax error or a broken verifier rule fails the
+      // whole module, as the reference's verifier and applyFullConversion do (VerifyAndAnnotate.cpp, DataflowLowering.cpp:799-816)
+      if (!d.unsupported) throw;
       fn.ops.clear();
       fn.rejected = true;
       fn.unsupported = d.unsupported;

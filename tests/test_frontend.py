@@ -209,17 +209,20 @@ def test_fusion_is_refused_when_it_would_change_the_result(nb):
 
 def test_linear_opdef_rule_products_need_a_constant_factor(nb):
     """checkApplyLike(requireLinearBody) of the reference (VerifyAndAnnotate.cpp:183-204): inside a linear_opdef a mulf
-    must have a constant operand and a divf a constant divisor.  The offending operator is rejected with the reference's
-    wording, the rest of the module still lowers; the same body in a func.func (variable coefficients) is legal."""
+    must have a constant operand and a divf a constant divisor.  The module is refused as a whole with the reference's
+    wording (a failed VerifyAndAnnotate fails the pass pipeline there too: only well-formed IR that is merely off the hot
+    path is set aside function by function); the same body in a func.func (variable coefficients) is legal."""
     import json
     import os
     pack = json.load(open(os.path.join(os.path.dirname(__file__), "golden", "reference_inputs.json")))
     text = pack["files"]["smoke_time_advance.mlir"]["text"]
     assert "%t  = arith.mulf %alpha, %lap0 : f64" in text
     bad = text.replace("%t  = arith.mulf %alpha, %lap0 : f64", "%t  = arith.mulf %x0, %lap0 : f64")
-    m = nb.Module(bad)
-    assert m.diagnostic("@ac_lap") is None
-    assert "MulFOp in linear region must multiply by a constant" in m.diagnostic("@ac_A")
+    with pytest.raises(nb.NeptuneError) as err:
+        nb.Module(bad)
+    assert "MulFOp in linear region must multiply by a constant" in str(err.value) and err.value.code == -1   # EINVAL
+    m = nb.Module(text)                                          # the untouched fixture: operators lower, @entry is set aside
+    assert m.diagnostic("@ac_lap") is None and m.diagnostic("@ac_A") is None and "time_advance" in m.diagnostic("@entry")
     m.destroy()
     m = nb.Module(H.program("varcoef_3d7", [8, 8, 8])[0])       # mulf(access, access) in a func.func: fine
     assert m.diagnostic("@entry") is None
