@@ -13,6 +13,7 @@
 #include <cuda.h>
 #include <cuda_runtime.h>
 #include <dlfcn.h>
+#include <fcntl.h>
 #include <nvrtc.h>
 #include <sys/stat.h>
 #include <unistd.h>
@@ -25,6 +26,7 @@
 #include <fstream>
 #include <map>
 #include <memory>
+#include <mutex>
 #include <sstream>
 
 #include "frontend/ir.h"
@@ -240,20 +242,79 @@ uint64_t header_digest(const std::string &csrc) {
   return h;
 }
 
+// The on-disk cache holds code that will be loaded into the GPU context, so it must be a directory only this user can
+// write: $NEPTUNE_B200_JIT_CACHE, else $HOME/.cache/neptune_b200_jit, else /tmp/neptune_b200_jit-<uid>; created with
+// mode 0700 and then checked (a real directory, owned by this user, no group/other write bit). If it is not, the cache
+// is simply off (empty string): every process compiles for itself.
 std::string cache_dir() {
   std::string d;
   if (const char *e = std::getenv("NEPTUNE_B200_JIT_CACHE")) d = e;
   else if (const char *h = std::getenv("HOME")) d = std::string(h) + "/.cache/neptune_b200_jit";
-  else d = "/tmp/neptune_b200_jit";
+  else d = "/tmp/neptune_b200_jit-" + std::to_string((long)geteuid());
+  while (d.size() > 1 && d.back() == '/') d.pop_back();
   std::string acc;
   for (size_t i = 0; i <= d.size(); ++i)
     if (i == d.size() || d[i] == '/') {
-      if (!acc.empty()) mkdir(acc.c_str(), 0755);
+      if (!acc.empty()) mkdir(acc.c_str(), i == d.size() ? 0700 : 0755);
       if (i < d.size()) acc += '/';
     } else {
       acc += d[i];
     }
+  struct stat st;
+  if (lstat(d.c_str(), &st) != 0 || !S_ISDIR(st.st_mode) || st.st_uid != geteuid() || (st.st_mode & (S_IWGRP | S_IWOTH))) return "";
   return d;
+}
+
+// One cache file per body: magic, digest of the generated source + compile options, the lowered kernel names, the
+// cubin, and a checksum of all of that. Names and code cannot be paired wrongly (one rename), a truncated or altered
+// file fails its checksum, and a file made from other source or options (a body_key collision, a change to the option
+// list below) fails the source digest: all of these read as a miss.
+const char CACHE_MAGIC[8] = {'N', 'B', 'J', 'I', 'T', '0', '0', '1'};
+
+bool cache_load(const std::string &path, uint64_t src_digest, size_t n_kernels, std::string &cubin, std::vector<std::string> &lowered) {
+  std::string blob;
+  if (!read_file(path, blob) || blob.size() < sizeof CACHE_MAGIC + 5 * 8) return false;
+  if (std::memcmp(blob.data(), CACHE_MAGIC, sizeof CACHE_MAGIC) != 0) return false;
+  uint64_t hdr[3], tail = 0;   // source digest, names bytes, cubin bytes
+  std::memcpy(hdr, blob.data() + 8, sizeof hdr);
+  const size_t body = 8 + sizeof hdr;
+  if (hdr[0] != src_digest || hdr[1] > blob.size() || hdr[2] > blob.size() || body + hdr[1] + hdr[2] + 8 != blob.size()) return false;
+  std::memcpy(&tail, blob.data() + blob.size() - 8, 8);
+  if (tail != fnv(1469598103934665603ull, blob.data(), blob.size() - 8)) return false;
+  std::istringstream is(blob.substr(body, (size_t)hdr[1]));
+  std::string l;
+  lowered.clear();
+  while (std::getline(is, l))
+    if (!l.empty()) lowered.push_back(l);
+  if (lowered.size() != n_kernels || hdr[2] == 0) { lowered.clear(); return false; }
+  cubin = blob.substr(body + (size_t)hdr[1], (size_t)hdr[2]);
+  return true;
+}
+
+void cache_store(const std::string &path, uint64_t src_digest, const std::string &cubin, const std::vector<std::string> &lowered) {
+  std::string names;
+  for (auto &l : lowered) names += l + "\n";
+  const uint64_t hdr[3] = {src_digest, (uint64_t)names.size(), (uint64_t)cubin.size()};
+  std::string blob(CACHE_MAGIC, sizeof CACHE_MAGIC);
+  blob.append((const char *)hdr, sizeof hdr);
+  blob += names;
+  blob += cubin;
+  const uint64_t tail = fnv(1469598103934665603ull, blob.data(), blob.size());
+  blob.append((const char *)&tail, 8);
+  // best effort; written under a temporary name (created exclusively, mode 0600) and renamed, so that a concurrent
+  // rank never reads half a file
+  const std::string tmp = path + ".tmp" + std::to_string((long)getpid());
+  const int fd = open(tmp.c_str(), O_WRONLY | O_CREAT | O_EXCL | O_NOFOLLOW, 0600);
+  if (fd < 0) return;
+  size_t done = 0;
+  while (done < blob.size()) {
+    const ssize_t w = write(fd, blob.data() + done, blob.size() - done);
+    if (w <= 0) break;
+    done += (size_t)w;
+  }
+  close(fd);
+  if (done == blob.size()) std::rename(tmp.c_str(), path.c_str());
+  else unlink(tmp.c_str());
 }
 
 // cubin + lowered kernel names, from the disk cache or from NVRTC
@@ -268,28 +329,23 @@ int compile_unit(const neptune_rt_stencil_desc &d, const std::vector<KernelSpec>
   const std::string csrc = csrc_dir();
   char tag[64];
   std::snprintf(tag, sizeof tag, "%016llx_%016llx", (unsigned long long)key, (unsigned long long)header_digest(csrc));
-  const std::string base = cache_dir() + "/body_" + tag;
-  std::string names;
-  if (read_file(base + ".cubin", out.cubin) && read_file(base + ".names", names) && !out.cubin.empty()) {
-    std::istringstream is(names);
-    std::string l;
-    while (std::getline(is, l))
-      if (!l.empty()) out.lowered.push_back(l);
-    if (out.lowered.size() == menu.size()) { out.from_cache = true; return NEPTUNE_RT_OK; }
-    out.lowered.clear();
-  }
+  const std::string dir = cache_dir();
+  const std::string path = dir.empty() ? std::string() : dir + "/body_" + tag + ".nbjit";
+  const std::string src = unit_source(d, menu, F);
+  const std::string inc = "-I" + csrc;
+  const char *opts[] = {"--gpu-architecture=sm_100a", "-std=c++17", "-lineinfo", "-default-device", inc.c_str()};
+  uint64_t src_digest = fnv(1469598103934665603ull, src.data(), src.size());
+  for (const char *o : opts) src_digest = fnv(src_digest, o, std::strlen(o) + 1);
+  if (!path.empty() && cache_load(path, src_digest, menu.size(), out.cubin, out.lowered)) { out.from_cache = true; return NEPTUNE_RT_OK; }
   NvrtcApi &n = nvrtc();
   if (!n.ok) {
     err = "this apply body is not in the prebuilt kernel catalogue and libnvrtc.so.12 could not be loaded to compile it";
     return NEPTUNE_RT_EUNSUPPORTED;
   }
-  const std::string src = unit_source(d, menu, F);
   nvrtcProgram prog;
   nvrtcResult r = n.CreateProgram(&prog, src.c_str(), ("body_" + std::string(tag) + ".cu").c_str(), 0, nullptr, nullptr);
   if (r != NVRTC_SUCCESS) { err = std::string("nvrtcCreateProgram: ") + n.GetErrorString(r); return NEPTUNE_RT_ECUDA; }
   for (auto &k : menu) n.AddNameExpression(prog, k.expr.c_str());
-  const std::string inc = "-I" + csrc;
-  const char *opts[] = {"--gpu-architecture=sm_100a", "-std=c++17", "-lineinfo", "-default-device", inc.c_str()};
   r = n.CompileProgram(prog, (int)(sizeof opts / sizeof opts[0]), opts);
   if (r != NVRTC_SUCCESS) {
     size_t ls = 0;
@@ -314,18 +370,7 @@ int compile_unit(const neptune_rt_stencil_desc &d, const std::vector<KernelSpec>
   out.cubin.assign(cs, '\0');
   n.GetCUBIN(prog, &out.cubin[0]);
   n.DestroyProgram(&prog);
-  // cache (best effort; written to a temporary name first so that a concurrent rank never reads half a file)
-  const std::string tmp = base + ".tmp" + std::to_string((long)getpid());
-  {
-    std::ofstream f(tmp + ".cubin", std::ios::binary);
-    f.write(out.cubin.data(), (std::streamsize)out.cubin.size());
-  }
-  {
-    std::ofstream f(tmp + ".names");
-    for (auto &l : out.lowered) f << l << "\n";
-  }
-  std::rename((tmp + ".names").c_str(), (base + ".names").c_str());
-  std::rename((tmp + ".cubin").c_str(), (base + ".cubin").c_str());
+  if (!path.empty()) cache_store(path, src_digest, out.cubin, out.lowered);
   return NEPTUNE_RT_OK;
 }
 
@@ -485,6 +530,8 @@ std::vector<std::unique_ptr<JitBody>> &jit_bodies() {
 }  // namespace
 
 int jit_body(const neptune_rt_stencil_desc &d, int device, bool compile_only, std::string &err, double *seconds) {
+  static std::mutex table_mutex;   // the JIT body table and its per-device modules: one compile / load at a time
+  std::lock_guard<std::mutex> table_lock(table_mutex);
   const auto t_begin = std::chrono::steady_clock::now();
   const uint64_t key = body_key(d);
   const BodyInfo bi = analyze_body(d);
