@@ -22,11 +22,12 @@ namespace mlir::Neptune::NeptuneIR {
 #define GEN_PASS_REGISTRATION
 #include "Passes/NeptuneIRB200Passes.h.inc"
 
-/// verify-annotate -> structure-lowering -> apply-to-b200 -> func/arith/memref to LLVM.
+/// verify-annotate -> structure-lowering -> apply-to-b200 -> scf-to-cf -> func/arith/cf/memref to LLVM.
 /// Registered as `neptuneir-to-b200` by registerNeptuneB200Pipelines().
 struct NeptuneToB200PipelineOptions : public PassPipelineOptions<NeptuneToB200PipelineOptions> {
   Option<bool> fma{*this, "fma", llvm::cl::desc("allow FMA contraction in the sweep kernels"), llvm::cl::init(false)};
-  Option<bool> fuse{*this, "fuse", llvm::cl::desc("fuse operator-call + AXPY apply pairs"), llvm::cl::init(true)};
+  // (no `fuse` option here: operator-call + AXPY fusion is a planner step of the MLIR-free front end,
+  //  neptune_b200_compile("neptuneir-to-b200{fuse=...}"); at the MLIR level every apply is lowered on its own)
 };
 void buildNeptuneToB200Pipeline(OpPassManager &pm, const NeptuneToB200PipelineOptions &options);
 void registerNeptuneB200Pipelines();

@@ -13,22 +13,24 @@
 // NOT COMPILED IN THIS REPOSITORY'S CI: the image has no MLIR.  Written against the MLIR API
 // level of the reference (llvm-project release/21.x); mlir/CMakeLists.txt builds it where find_package(MLIR) succeeds.
 //
-// Two declarations are expected from the reference tree (a four-line refactor of DataflowLowering.cpp, which keeps
-// them in an anonymous namespace today):
-//     class NeptuneIRTypeConverter;                                   (DataflowLowering.cpp:51-71)
+// Two functions are expected from the reference tree. DataflowLowering.cpp keeps its type converter and patterns in an
+// anonymous namespace today; mlir/patches/0001-export-dataflow-patterns.patch (pure additions, `git apply` it in the
+// reference checkout; tests/test_mlir_sources.py checks that it still applies) exports them through a new header:
+//     std::unique_ptr<TypeConverter> createNeptuneIRTypeConverter(MLIRContext *);    (the class at :51-71)
 //     void populateNeptuneIRStoragePatterns(RewritePatternSet &, TypeConverter &);   (the list at :790-797)
 //
 //===----------------------------------------------------------------------===//
 #include "Dialect/NeptuneIR/NeptuneIRDialect.h"
 #include "Dialect/NeptuneIR/NeptuneIROps.h"
 #include "Passes/NeptuneIRB200Passes.h"
-#include "Passes/NeptuneIRDataflowPatterns.h"   // NeptuneIRTypeConverter, populateNeptuneIRStoragePatterns
+#include "Passes/NeptuneIRDataflowPatterns.h"   // createNeptuneIRTypeConverter, populateNeptuneIRStoragePatterns
 
 #include "mlir/Dialect/Arith/IR/Arith.h"
 #include "mlir/Dialect/Func/IR/FuncOps.h"
 #include "mlir/Dialect/Func/Transforms/FuncConversions.h"
 #include "mlir/Dialect/LLVMIR/LLVMDialect.h"
 #include "mlir/Dialect/MemRef/IR/MemRef.h"
+#include "mlir/Dialect/SCF/IR/SCF.h"
 #include "mlir/IR/BuiltinOps.h"
 #include "mlir/Transforms/DialectConversion.h"
 
@@ -223,8 +225,13 @@ struct ApplyToB200Lowering : OpConversionPattern<ApplyOp> {
     if (need <= 0) return op.emitOpError("the apply could not be described to the B200 runtime");
     std::string blob(static_cast<size_t>(need), '\0');
     neptune_rt_desc_pack(&desc, blob.data(), need);
-    char name[64];
-    std::snprintf(name, sizeof name, "__neptune_b200_desc_%016llx_%u", (unsigned long long)neptune_rt_body_key(&desc), nextId());
+    // named by content (structure key + FNV-1a of the packed bytes): no counter shared between pattern applications,
+    // the same name whatever order the applies are visited in, and identical descriptors share one global
+    uint64_t digest = 1469598103934665603ull;
+    for (unsigned char ch : blob) { digest ^= ch; digest *= 1099511628211ull; }
+    char name[80];
+    std::snprintf(name, sizeof name, "__neptune_b200_desc_%016llx_%016llx", (unsigned long long)neptune_rt_body_key(&desc),
+                  (unsigned long long)digest);
     Value descPtr = getOrCreateDescGlobal(op, rewriter, loc, name, blob);
 
     // 3. the calls
@@ -252,10 +259,6 @@ struct ApplyToB200Lowering : OpConversionPattern<ApplyOp> {
   }
 
 private:
-  static unsigned nextId() {
-    static unsigned id = 0;
-    return id++;
-  }
   /// The runtime takes fully dynamic memrefs of the apply's rank (memref<?x?x?xf64>): one C signature per rank.
   static MemRefType UnrankedOrRanked(MemRefType t) {
     SmallVector<int64_t> dyn(t.getRank(), ShapedType::kDynamic);
@@ -277,10 +280,12 @@ struct NeptuneIRApplyToB200Pass final : public mlir::Neptune::NeptuneIR::impl::N
   void runOnOperation() override {
     ModuleOp module = getOperation();
     MLIRContext *ctx = module.getContext();
-    NeptuneIRTypeConverter typeConverter(ctx);
+    std::unique_ptr<TypeConverter> converterOwner = createNeptuneIRTypeConverter(ctx);
+    TypeConverter &typeConverter = *converterOwner;
 
     ConversionTarget target(*ctx);
-    target.addLegalDialect<BuiltinDialect, arith::ArithDialect, memref::MemRefDialect, func::FuncDialect, LLVM::LLVMDialect>();
+    target.addLegalDialect<BuiltinDialect, arith::ArithDialect, memref::MemRefDialect, scf::SCFDialect, func::FuncDialect,
+                           LLVM::LLVMDialect>();   // scf: what ReduceLowering emits; the pipeline lowers it afterwards
     target.addIllegalDialect<NeptuneIRDialect>();
     target.markUnknownOpDynamicallyLegal([&](Operation *op) { return typeConverter.isLegal(op); });
     target.addDynamicallyLegalOp<func::FuncOp>([&](func::FuncOp f) {
@@ -300,8 +305,8 @@ struct NeptuneIRApplyToB200Pass final : public mlir::Neptune::NeptuneIR::impl::N
     // the sweep
     patterns.add<ApplyToB200Lowering>(typeConverter, ctx, fma);
 
-    // (option `fuse`: operator-call + AXPY fusion happens inside the runtime's planner when the module is driven
-    //  through neptune_b200_compile; at the MLIR level the two applies are lowered one by one.)
+    // (operator-call + AXPY fusion is a planner step of the MLIR-free front end, neptune_b200_compile; here every apply
+    //  is lowered on its own, so the pass has no `fuse` option)
     if (failed(applyFullConversion(module, target, std::move(patterns)))) signalPassFailure();
   }
 };

@@ -1,8 +1,9 @@
 //===- NeptuneIRToB200Pipeline.cpp - the `neptuneir-to-b200` pipeline ---------------------===//
 //
 // Shape: lib/Pipeline/NeptuneIRPassesPipeline.cpp:5-53 of the reference (buildNeptuneToLLVMPipeline +
-// registerNeptunePipelines).  Differences: no runtime-lowering (PETSc) stage and no SCF stage — an apply becomes
-// runtime calls, not loops — and the dataflow stage is `neptune-ir-apply-to-b200`.
+// registerNeptunePipelines).  Differences: no runtime-lowering (PETSc) stage, and the dataflow stage is
+// `neptune-ir-apply-to-b200`: an apply becomes runtime calls, not loops.  The SCF stage stays, because the storage
+// patterns shared with the reference include ReduceLowering, which builds scf.for (DataflowLowering.cpp:608-637).
 //
 // Call registerNeptuneB200Pipelines() next to registerNeptunePipelines() in src/neptuneOpt.cpp:44 and in
 // NeptuneCompiler's constructor; `neptune-opt in.mlir --neptuneir-to-b200` then works like `--neptuneir-to-llvm`.
@@ -16,6 +17,7 @@
 #include "mlir/Conversion/FuncToLLVM/ConvertFuncToLLVMPass.h"
 #include "mlir/Conversion/MemRefToLLVM/MemRefToLLVM.h"
 #include "mlir/Conversion/ReconcileUnrealizedCasts/ReconcileUnrealizedCasts.h"
+#include "mlir/Conversion/SCFToControlFlow/SCFToControlFlow.h"
 #include "mlir/Transforms/Passes.h"
 
 using namespace mlir;
@@ -31,13 +33,14 @@ void mlir::Neptune::NeptuneIR::buildNeptuneToB200Pipeline(OpPassManager &pm, con
   {
     NeptuneIRApplyToB200PassOptions opt;
     opt.fma = options.fma;
-    opt.fuse = options.fuse;
     pm.addPass(createNeptuneIRApplyToB200Pass(opt));
   }
   pm.addPass(createCanonicalizerPass());
   pm.addPass(createCSEPass());
 
-  // 2) what is left is func / arith / memref / llvm.global: the tail of buildNeptuneToLLVMPipeline (:28-46)
+  // 2) what is left is func / arith / memref / llvm.global, plus scf.for where the module held a neptune_ir.reduce:
+  //    the tail of buildNeptuneToLLVMPipeline (:28-46), SCF stage included
+  pm.addPass(createSCFToControlFlowPass());
   pm.addPass(createArithToLLVMConversionPass());
   pm.addPass(createConvertControlFlowToLLVMPass());
   pm.addPass(createFinalizeMemRefToLLVMConversionPass());
