@@ -694,6 +694,82 @@ def test_committed_golden_fixtures_on_device(nb, ctx):
         assert H.bits_equal([b, a][res], g["result"]), f
 
 
+@pytest.mark.parametrize("name,shape,ty,steps", [
+    ("jacobi_star", (768, 768, 768), "f64", 4),        # BASELINE configs[4] (C5) on one GPU, fp64
+    ("jacobi_star", (768, 768, 768), "f32", 4),        # ... fp32
+    ("jacobi_star", (96, 768, 768), "f64", 4),         # ... one GPU's share of 768^3 over 8 GPUs
+    ("varcoef_3d27", (128, 1024, 1024), "f64", 2),     # BASELINE configs[3] (C4): one GPU's share of 1024^3 over 8, 27 coefficient fields
+])
+def test_full_size_properties_with_extra_inputs(nb, ctx, name, shape, ty, steps):
+    """C4 and C5 at BASELINE.json's per-GPU sizes (the bodies with pointwise extra inputs), through properties that do
+    not need the oracle on the whole box, all bitwise:
+      * every kernel family agrees: the default path (fused pairs where the body has them) == single sweeps == the
+        direct kernel;
+      * linearity under an exact scaling of the state (and of the right-hand side): step(2u, 2f) == 2 step(u, f);
+      * the shell is copied through;
+      * a band of planes in the middle equals the oracle run on the band's dependency cone (extra inputs cut alike).
+    Coefficient fields are made one at a time and only their cone rows stay on the host."""
+    dt = H.NPT[ty]
+    text, n_extra = H.program(name, list(shape), ty)
+    rng = np.random.default_rng(20260407)
+    u = rng.uniform(-1, 1, size=shape).astype(dt)
+    mid = shape[0] // 2
+    rows = slice(mid - 2 * steps, mid + 2 * steps)
+    corner = (rows, slice(0, 96), slice(0, 160))
+    scale_extra = name == "jacobi_star"                # the rhs enters additively: it scales with the state
+    m = nb.Module(text)
+    extra, extra_cone = [], []
+    try:
+        st = m.stencil(ctx, 0)
+        for k in range(n_extra):
+            c = (rng.uniform(-1, 1, size=shape) if scale_extra else rng.uniform(0.5, 1.5, size=shape) / n_extra).astype(dt)
+            extra.append(nb.Field.from_numpy(ctx, c))
+            extra_cone.append(np.ascontiguousarray(c[corner]))
+            del c
+        fa, fb = nb.Field.from_numpy(ctx, u), nb.Field.from_numpy(ctx, u)
+        first = st.run_steps(fa, fb, extra, steps).download()
+        fusable = name == "jacobi_star"
+        assert st.variant().startswith("tb2") == fusable, st.variant()
+        if fusable:
+            st.set("tblock", 1)
+            fa.upload(u); fb.upload(u)
+            single = st.run_steps(fa, fb, extra, steps).download()
+            assert not st.variant().startswith("tb2")
+            assert H.bits_equal(first, single), "temporally blocked != single sweeps"
+            del single
+        st.set("variant", "direct")
+        fa.upload(u); fb.upload(u)
+        direct = st.run_steps(fa, fb, extra, steps).download()
+        assert st.variant() == "direct" and H.bits_equal(direct, first), "staged kernel != direct kernel"
+        del direct
+        st.set("variant", "auto"); st.set("tblock", 0)
+        two = dt(2.0)
+        fa.upload(two * u); fb.upload(two * u)
+        if scale_extra:
+            for f in extra:
+                f.upload(two * f.download())
+        twice = st.run_steps(fa, fb, extra, steps).download()
+        assert H.bits_equal(twice, two * first), "step(2u) != 2 step(u)"
+        del twice
+        for d in range(3):
+            lo = [slice(None)] * 3; hi = [slice(None)] * 3
+            lo[d] = 0; hi[d] = -1
+            assert H.bits_equal(first[tuple(lo)], u[tuple(lo)]) and H.bits_equal(first[tuple(hi)], u[tuple(hi)])
+        fa.free(); fb.free()
+    finally:
+        for f in extra:
+            f.free()
+        m.destroy()
+    cone = np.ascontiguousarray(u[corner])
+    ctext, _ = H.program(name, list(cone.shape), ty)
+    if name == "jacobi_star":                          # the builder derives h^2 from the extents: keep the full box's value
+        ctext = H.mb.jacobi_star(list(cone.shape), 1.0 / (max(shape) ** 2), ty)
+    want = H.oracle_steps(ctext, cone, extra_cone, steps)
+    got = first[corner]
+    inner = (slice(steps, 3 * steps), slice(0, 96 - steps), slice(0, 160 - steps))
+    assert H.bits_equal(np.ascontiguousarray(got[inner]), np.ascontiguousarray(want[inner]))
+
+
 @pytest.mark.parametrize("name,shape", [
     ("heat_star", (512, 512, 512)),       # BASELINE configs[2] (C3), one GPU's share
     ("heat_box_2d9", (16384, 16384)),     # BASELINE configs[1] (C2)
